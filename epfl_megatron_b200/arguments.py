@@ -1,0 +1,427 @@
+"""Command-line surface: one flat Namespace with the reference's underscore flag names.
+
+The flag set, defaults and derivations follow megatron/arguments.py (groups :367-1073,
+validation :52-345) so launch scripts written for the reference work unchanged. The
+declaration is table-driven here; B200-specific switches live in their own group.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+
+import torch
+
+from .models.enums import PositionEmbeddingType
+
+GLU_CHOICES = ("liglu", "geglu", "reglu", "swiglu")
+
+T, F = "store_true", "store_false"
+
+
+def _pos_type(x):
+    return x if isinstance(x, PositionEmbeddingType) else PositionEmbeddingType[x]
+
+
+# (flag, kwargs). ``action`` T/F are store_true / store_false.
+_GROUPS = {
+    "Transformer-Engine": [
+        ("--fp8_e4m3", dict(action=T)), ("--fp8_hybrid", dict(action=T)),
+        ("--no_fp8_wgrad", dict(action=F, dest="fp8_wgrad")),
+        ("--fp8_margin", dict(type=int, default=0)), ("--fp8_interval", dict(type=int, default=1)),
+        ("--transformer_impl", dict(default="local", choices=["local", "transformer_engine"])),
+        ("--fp8_amax_history_len", dict(type=int, default=1)),
+        ("--fp8_amax_compute_algo", dict(default="most_recent", choices=["most_recent", "max"])),
+    ],
+    "inference": [
+        ("--inference_batch_times_seqlen_threshold", dict(type=int, default=512)),
+        ("--max_tokens_to_oom", dict(type=int, default=12000)),
+    ],
+    "network size": [
+        ("--num_layers", dict(type=int)), ("--encoder_num_layers", dict(type=int)),
+        ("--decoder_num_layers", dict(type=int)), ("--hidden_size", dict(type=int)),
+        ("--ffn_hidden_size", dict(type=int)), ("--num_attention_heads", dict(type=int)),
+        ("--num_attention_heads_kv", dict(type=int)), ("--kv_channels", dict(type=int)),
+        ("--max_position_embeddings", dict(type=int)),
+        ("--make_vocab_size_divisible_by", dict(type=int, default=128)),
+        ("--layernorm_epsilon", dict(type=float, default=1e-5)),
+        ("--apply_residual_connection_post_layernorm", dict(action=T)),
+        ("--use_bias", dict(action=T)), ("--use_rms_norm", dict(action=T)),
+        ("--use_post_ln", dict(action=T)), ("--onnx_safe", dict(type=bool, required=False)),
+        ("--glu_activation", dict(type=str, choices=list(GLU_CHOICES))),
+        ("--position_embedding_type", dict(type=_pos_type, choices=list(PositionEmbeddingType),
+                                           default=PositionEmbeddingType.absolute)),
+        ("--rope_scaling_factor", dict(type=float, default=1.0)),
+        ("--parallel_attn", dict(action=T)), ("--parallel_layernorm", dict(action=T)),
+        ("--no_tie_embed_logits", dict(action=F, dest="tie_embed_logits")),
+    ],
+    "logging": [
+        ("--log_params_norm", dict(action=T)), ("--log_num_zeros_in_grad", dict(action=T)),
+        ("--timing_log_level", dict(type=int, default=0, choices=range(0, 3))),
+        # reference quirk kept: passing the flag turns the barrier OFF (arguments.py:492)
+        ("--barrier_with_L1_time", dict(action=F)),
+        ("--timing_log_option", dict(type=str, default="minmax", choices=["max", "minmax", "all"])),
+        ("--tensorboard_log_interval", dict(type=int, default=1)),
+        ("--tensorboard_queue_size", dict(type=int, default=1000)),
+        ("--log_timers_to_tensorboard", dict(action=T)),
+        ("--log_batch_size_to_tensorboard", dict(action=T)),
+        ("--log_validation_ppl_to_tensorboard", dict(action=T)),
+        ("--log_memory_to_tensorboard", dict(action=T)),
+        ("--log_world_size_to_tensorboard", dict(action=T)),
+        ("--wandb_logger", dict(action=T)), ("--wandb_project", dict(type=str)),
+        ("--wandb_entity", dict(type=str, default="meditron")), ("--wandb_id", dict(type=str)),
+        ("--wandb_resume", dict(action=T)), ("--wandb_api_key", dict(type=str)),
+    ],
+    "regularization": [
+        ("--attention_dropout", dict(type=float, default=0.1)),
+        ("--hidden_dropout", dict(type=float, default=0.1)), ("--lima_dropout", dict(action=T)),
+        ("--weight_decay", dict(type=float, default=0.01)),
+        ("--start_weight_decay", dict(type=float)), ("--end_weight_decay", dict(type=float)),
+        ("--weight_decay_incr_style", dict(type=str, default="constant",
+                                           choices=["constant", "linear", "cosine"])),
+        ("--clip_grad", dict(type=float, default=1.0)), ("--adam_beta1", dict(type=float, default=0.9)),
+        ("--adam_beta2", dict(type=float, default=0.999)), ("--adam_eps", dict(type=float, default=1e-8)),
+        ("--sgd_momentum", dict(type=float, default=0.9)),
+    ],
+    "training": [
+        ("--micro_batch_size", dict(type=int)), ("--global_batch_size", dict(type=int)),
+        ("--rampup_batch_size", dict(nargs="*")), ("--recompute_activations", dict(action=T)),
+        ("--recompute_granularity", dict(type=str, choices=["full", "selective"])),
+        ("--distribute_saved_activations", dict(action=T)),
+        ("--recompute_method", dict(type=str, choices=["uniform", "block"])),
+        ("--recompute_num_layers", dict(type=int, default=1)),
+        ("--train_iters", dict(type=int)), ("--train_samples", dict(type=int)),
+        ("--log_interval", dict(type=int, default=100)), ("--exit_interval", dict(type=int)),
+        ("--exit_duration_in_mins", dict(type=int)), ("--exit_signal_handler", dict(action=T)),
+        ("--tensorboard_dir", dict(type=str)),
+        ("--no_masked_softmax_fusion", dict(action=F, dest="masked_softmax_fusion")),
+        ("--no_bias_gelu_fusion", dict(action=F, dest="bias_gelu_fusion")),
+        ("--no_bias_dropout_fusion", dict(action=F, dest="bias_dropout_fusion")),
+        ("--use_flash_attn", dict(action=T)),
+        ("--optimizer", dict(type=str, default="adam", choices=["adam", "sgd"])),
+        ("--dataloader_type", dict(type=str, choices=["single", "cyclic"])),
+        ("--no_async_tensor_model_parallel_allreduce",
+         dict(action=F, dest="async_tensor_model_parallel_allreduce")),
+        ("--no_persist_layer_norm", dict(action=T)), ("--sequence_parallel", dict(action=T)),
+        ("--no_gradient_accumulation_fusion", dict(action=F, dest="gradient_accumulation_fusion")),
+    ],
+    "initialization": [
+        ("--seed", dict(type=int, default=1234)), ("--data_parallel_random_init", dict(action=T)),
+        ("--init_method_std", dict(type=float, default=0.02)),
+        ("--init_method_xavier_uniform", dict(action=T)),
+    ],
+    "learning rate": [
+        ("--lr", dict(type=float)),
+        ("--lr_decay_style", dict(type=str, default="linear",
+                                  choices=["constant", "linear", "cosine", "inverse-square-root"])),
+        ("--lr_decay_iters", dict(type=int)), ("--lr_decay_samples", dict(type=int)),
+        ("--lr_warmup_fraction", dict(type=float)), ("--lr_warmup_iters", dict(type=int, default=0)),
+        ("--lr_warmup_samples", dict(type=int, default=0)), ("--min_lr", dict(type=float, default=0.0)),
+        ("--override_opt_param_scheduler", dict(action=T)),
+        ("--use_checkpoint_opt_param_scheduler", dict(action=T)),
+    ],
+    "checkpointing": [
+        ("--save", dict(type=str)), ("--save_interval", dict(type=int)),
+        ("--no_save_optim", dict(action=T, default=None)), ("--no_save_rng", dict(action=T, default=None)),
+        ("--load", dict(type=str)), ("--no_load_optim", dict(action=T, default=None)),
+        ("--no_load_rng", dict(action=T, default=None)), ("--finetune", dict(action=T)),
+        ("--no_initialization", dict(action=F, dest="perform_initialization")),
+        ("--use_checkpoint_args", dict(action=T)),
+    ],
+    "mixed precision": [
+        ("--fp16", dict(action=T)), ("--bf16", dict(action=T)), ("--loss_scale", dict(type=float)),
+        ("--initial_loss_scale", dict(type=float, default=2 ** 32)),
+        ("--min_loss_scale", dict(type=float, default=1.0)),
+        ("--loss_scale_window", dict(type=float, default=1000)),
+        ("--hysteresis", dict(type=int, default=2)), ("--fp32_residual_connection", dict(action=T)),
+        ("--no_query_key_layer_scaling", dict(action=F, dest="apply_query_key_layer_scaling")),
+        ("--attention_softmax_in_fp32", dict(action=T)),
+        ("--accumulate_allreduce_grads_in_fp32", dict(action=T)),
+        ("--fp16_lm_cross_entropy", dict(action=T)),
+    ],
+    "distributed": [
+        ("--tensor_model_parallel_size", dict(type=int, default=1)),
+        ("--pipeline_model_parallel_size", dict(type=int, default=1)),
+        ("--pipeline_model_parallel_split_rank", dict(type=int)),
+        ("--num_layers_per_virtual_pipeline_stage", dict(type=int)),
+        ("--distributed_backend", dict(default="nccl", choices=["nccl", "gloo"])),
+        ("--DDP_impl", dict(default="local", choices=["local", "torch"])),
+        ("--no_contiguous_buffers_in_local_ddp",
+         dict(action=F, dest="use_contiguous_buffers_in_local_ddp")),
+        ("--no_scatter_gather_tensors_in_pipeline",
+         dict(action=F, dest="scatter_gather_tensors_in_pipeline")),
+        ("--use_ring_exchange_p2p", dict(action=T, default=False)),
+        ("--local_rank", dict(type=int)), ("--use_cpu_initialization", dict(action=T, default=None)),
+        ("--empty_unused_memory_level", dict(default=0, type=int, choices=[0, 1, 2])),
+        ("--standalone_embedding_stage", dict(action=T, default=False)),
+        ("--use_distributed_optimizer", dict(action=T)),
+    ],
+    "validation": [
+        ("--eval_iters", dict(type=int, default=100)), ("--eval_interval", dict(type=int, default=1000)),
+    ],
+    "data and dataloader": [
+        ("--data_path", dict(nargs="*")), ("--split", dict(type=str, default="969, 30, 1")),
+        ("--train_data_path", dict(nargs="*")), ("--valid_data_path", dict(nargs="*")),
+        ("--test_data_path", dict(nargs="*")), ("--vocab_file", dict(type=str)),
+        ("--merge_file", dict(type=str)), ("--vocab_extra_ids", dict(type=int, default=0)),
+        ("--vocab_extra_ids_list", dict(type=str)), ("--seq_length", dict(type=int)),
+        ("--encoder_seq_length", dict(type=int)), ("--decoder_seq_length", dict(type=int)),
+        ("--retriever_seq_length", dict(type=int, default=256)),
+        ("--sample_rate", dict(type=float, default=1.0)), ("--mask_prob", dict(type=float, default=0.15)),
+        ("--short_seq_prob", dict(type=float, default=0.1)), ("--mmap_warmup", dict(action=T)),
+        ("--num_workers", dict(type=int, default=2)),
+        ("--tokenizer_type", dict(type=str, choices=[
+            "BertWordPieceLowerCase", "BertWordPieceCase", "GPT2BPETokenizer",
+            "SentencePieceTokenizer", "FalconTokenizer", "NullTokenizer"])),
+        ("--tokenizer_model", dict(type=str)),
+        ("--no_new_tokens", dict(action=F, dest="new_tokens")),
+        ("--data_impl", dict(type=str, default="infer", choices=["lazy", "cached", "mmap", "infer"])),
+        ("--reset_position_ids", dict(action=T)), ("--reset_attention_mask", dict(action=T)),
+        ("--eod_mask_loss", dict(action=T)),
+    ],
+    "autoresume": [
+        ("--adlr_autoresume", dict(action=T)), ("--adlr_autoresume_interval", dict(type=int, default=1000)),
+    ],
+    "biencoder": [
+        ("--ict_head_size", dict(type=int)), ("--biencoder_projection_dim", dict(type=int, default=0)),
+        ("--biencoder_shared_query_context_model", dict(action=T)), ("--ict_load", dict(type=str)),
+        ("--bert_load", dict(type=str)), ("--titles_data_path", dict(type=str)),
+        ("--query_in_block_prob", dict(type=float, default=0.1)), ("--use_one_sent_docs", dict(action=T)),
+        ("--evidence_data_path", dict(type=str)),
+        ("--retriever_report_topk_accuracies", dict(nargs="+", type=int, default=[])),
+        ("--retriever_score_scaling", dict(action=T)), ("--block_data_path", dict(type=str)),
+        ("--embedding_path", dict(type=str)), ("--indexer_batch_size", dict(type=int, default=128)),
+        ("--indexer_log_interval", dict(type=int, default=1000)),
+    ],
+    "vision": [
+        ("--num_classes", dict(type=int, default=1000)), ("--img_h", dict(type=int, default=224)),
+        ("--img_w", dict(type=int, default=224)), ("--num_channels", dict(type=int, default=3)),
+        ("--patch_dim", dict(type=int, default=16)), ("--classes_fraction", dict(type=float, default=1.0)),
+        ("--data_per_class_fraction", dict(type=float, default=1.0)),
+        ("--no_data_sharding", dict(action=F, dest="data_sharding")),
+        ("--head_lr_mult", dict(type=float, default=1.0)), ("--iter_per_epoch", dict(type=int, default=1250)),
+        ("--dino_local_img_size", dict(type=int, default=96)),
+        ("--dino_local_crops_number", dict(type=int, default=10)),
+        ("--dino_head_hidden_size", dict(type=int, default=2048)),
+        ("--dino_bottleneck_size", dict(type=int, default=256)),
+        ("--dino_freeze_last_layer", dict(type=float, default=1)),
+        ("--dino_norm_last_layer", dict(action=T)),
+        ("--dino_warmup_teacher_temp", dict(type=float, default=0.04)),
+        ("--dino_teacher_temp", dict(type=float, default=0.07)),
+        ("--dino_warmup_teacher_temp_epochs", dict(type=int, default=30)),
+    ],
+    # ---- additions of this framework (no counterpart in the reference) ----
+    "b200": [
+        ("--synthetic_data", dict(action=T)),            # random tokens instead of --data_path
+        ("--b200_kernels", dict(default="auto", choices=["auto", "on", "off"])),
+        ("--b200_gemm", dict(default="auto", choices=["auto", "own", "cublas"])),
+        ("--b200_fused_comm", dict(default="auto", choices=["auto", "on", "off"])),
+        ("--ddp_bucket_mb", dict(type=int, default=256)),
+        ("--no_overlap_grad_reduce", dict(action=F, dest="overlap_grad_reduce")),
+        ("--log_throughput", dict(action=T)), ("--metrics_jsonl", dict(type=str)),
+        ("--bert_binary_head", dict(action=T, default=True)),
+        ("--log_learning_rate_to_tensorboard", dict(type=bool, default=True)),
+        ("--log_loss_scale_to_tensorboard", dict(type=bool, default=True)),
+        ("--fault_inject", dict(type=str)),               # test hook, see utils/fault.py
+    ],
+}
+
+
+def build_base_parser() -> argparse.ArgumentParser:
+    parser = argparse.ArgumentParser(description="B200 Megatron-LLM arguments", allow_abbrev=False)
+    for title, flags in _GROUPS.items():
+        grp = parser.add_argument_group(title=title)
+        for flag, kw in flags:
+            grp.add_argument(flag, **kw)
+    return parser
+
+
+def parse_args(extra_args_provider=None, ignore_unknown_args=False, args_list=None):
+    parser = build_base_parser()
+    if extra_args_provider is not None:
+        parser = extra_args_provider(parser)
+    if ignore_unknown_args:
+        args, _ = parser.parse_known_args(args_list)
+    else:
+        args = parser.parse_args(args_list)
+    args.rank = int(os.getenv("RANK", "0"))
+    args.world_size = int(os.getenv("WORLD_SIZE", "1"))
+    return args
+
+
+def _require(cond, msg):
+    if not cond:
+        raise AssertionError(msg)
+
+
+def validate_args(args, defaults=None):
+    """Cross-flag checks and derived values (behaviour of megatron/arguments.py:52-345)."""
+    defaults = defaults or {}
+    say = (lambda *a: print(*a, flush=True)) if args.rank == 0 else (lambda *a: None)
+
+    ws = args.world_size
+    args.tensor_model_parallel_size = min(args.tensor_model_parallel_size, ws)
+    _require(ws % args.tensor_model_parallel_size == 0,
+             f"world size ({ws}) is not divisible by tensor model parallel size")
+    args.pipeline_model_parallel_size = min(args.pipeline_model_parallel_size,
+                                            ws // args.tensor_model_parallel_size)
+    args.transformer_pipeline_model_parallel_size = (
+        args.pipeline_model_parallel_size - 1 if args.standalone_embedding_stage
+        else args.pipeline_model_parallel_size)
+    mp = args.pipeline_model_parallel_size * args.tensor_model_parallel_size
+    _require(ws % mp == 0, f"world size {ws} not divisible by tp*pp = {mp}")
+    args.data_parallel_size = ws // mp
+    say(f"using world size: {ws}, data-parallel-size: {args.data_parallel_size}, "
+        f"tensor-model-parallel size: {args.tensor_model_parallel_size}, "
+        f"pipeline-model-parallel size: {args.pipeline_model_parallel_size} ")
+    if args.pipeline_model_parallel_size > 1 and args.pipeline_model_parallel_split_rank is not None:
+        _require(args.pipeline_model_parallel_split_rank < args.pipeline_model_parallel_size,
+                 "split rank needs to be less than pipeline model parallel size")
+
+    if getattr(args, "recompute_activations", False):
+        args.recompute_granularity = "selective"
+    if hasattr(args, "recompute_activations"):
+        del args.recompute_activations
+
+    for key, val in defaults.items():
+        if getattr(args, key, None) is not None:
+            say(f"WARNING: overriding default arguments for {key}:{val} with {key}:{getattr(args, key)}")
+        else:
+            setattr(args, key, val)
+
+    _require(args.micro_batch_size is not None and args.micro_batch_size > 0, "micro_batch_size")
+    if args.global_batch_size is None:
+        args.global_batch_size = args.micro_batch_size * args.data_parallel_size
+        say(f"setting global batch size to {args.global_batch_size}")
+    _require(args.global_batch_size > 0, "global_batch_size")
+
+    # layer count aliases (needed before the virtual pipeline derivation)
+    if args.num_layers is not None:
+        _require(args.encoder_num_layers is None, "cannot have both num_layers and encoder_num_layers")
+        args.encoder_num_layers = args.num_layers
+    else:
+        _require(args.encoder_num_layers is not None, "either num_layers or encoder_num_layers needed")
+        args.num_layers = args.encoder_num_layers
+
+    if args.num_layers_per_virtual_pipeline_stage is not None:
+        # The reference demands pp > 2 (arguments.py:117-120); interleaving is well defined
+        # for pp == 2 as well, which BASELINE config 3 needs, so only pp >= 2 is required.
+        _require(args.pipeline_model_parallel_size >= 2,
+                 "interleaved schedule needs pipeline-model-parallel size >= 2")
+        _require(args.num_layers % args.num_layers_per_virtual_pipeline_stage == 0,
+                 "num_layers not divisible by num_layers_per_virtual_pipeline_stage")
+        args.virtual_pipeline_model_parallel_size = (
+            (args.num_layers // args.transformer_pipeline_model_parallel_size)
+            // args.num_layers_per_virtual_pipeline_stage)
+    else:
+        args.virtual_pipeline_model_parallel_size = None
+
+    args.params_dtype = torch.float
+    if args.fp16:
+        _require(not args.bf16, "fp16 and bf16 are exclusive")
+        args.params_dtype = torch.half
+    if args.bf16:
+        args.params_dtype = torch.bfloat16
+        if not args.accumulate_allreduce_grads_in_fp32:
+            args.accumulate_allreduce_grads_in_fp32 = True
+            say("accumulate and all-reduce gradients in fp32 for bfloat16 data type.")
+    say(f"using {args.params_dtype} for parameters ...")
+
+    if args.accumulate_allreduce_grads_in_fp32 or args.use_distributed_optimizer:
+        _require(args.DDP_impl == "local", "fp32 grad accumulation / dist-opt need --DDP_impl local")
+        _require(args.use_contiguous_buffers_in_local_ddp, "contiguous grad buffer required")
+    if args.DDP_impl == "torch":
+        args.use_contiguous_buffers_in_local_ddp = False
+    if args.dataloader_type is None:
+        args.dataloader_type = "single"
+
+    args.consumed_train_samples = 0
+    args.consumed_valid_samples = 0
+    args.variable_seq_lengths = False
+
+    if args.train_iters:
+        _require(args.train_samples is None, "expected iteration-based training")
+        _require(args.lr_decay_samples is None, "expected iteration-based learning rate decay")
+        _require(args.lr_warmup_samples == 0, "expected iteration-based learning rate warmup")
+        _require(args.rampup_batch_size is None, "no batch-size rampup for iteration-based training")
+        if args.lr_warmup_fraction is not None:
+            _require(args.lr_warmup_iters == 0, "only one of lr_warmup_fraction / lr_warmup_iters")
+    if args.train_samples:
+        _require(args.train_iters is None, "expected sample-based training")
+        _require(args.lr_decay_iters is None, "expected sample-based learning rate decay")
+        _require(args.lr_warmup_iters == 0, "expected sample-based learning rate warmup")
+        if args.lr_warmup_fraction is not None:
+            _require(args.lr_warmup_samples == 0, "only one of lr_warmup_fraction / lr_warmup_samples")
+
+    for req in ("num_layers", "hidden_size", "num_attention_heads"):
+        _require(getattr(args, req) is not None, f"{req} argument is None")
+    if args.ffn_hidden_size is None:
+        args.ffn_hidden_size = 4 * args.hidden_size
+    if args.kv_channels is None:
+        _require(args.hidden_size % args.num_attention_heads == 0, "hidden % heads")
+        args.kv_channels = args.hidden_size // args.num_attention_heads
+    if args.num_attention_heads_kv is None:
+        args.num_attention_heads_kv = args.num_attention_heads
+    if args.seq_length is not None:
+        _require(args.encoder_seq_length is None, "seq_length and encoder_seq_length both set")
+        args.encoder_seq_length = args.seq_length
+    else:
+        _require(args.encoder_seq_length is not None, "seq_length missing")
+        args.seq_length = args.encoder_seq_length
+
+    args.position_embedding_type = _pos_type(args.position_embedding_type)
+    _require(args.max_position_embeddings is not None, "max_position_embeddings missing")
+    _require(args.max_position_embeddings >= args.seq_length, "max_position_embeddings < seq_length")
+    if args.decoder_seq_length is not None:
+        _require(args.max_position_embeddings >= args.decoder_seq_length, "decoder_seq_length")
+    _require(args.rope_scaling_factor >= 1, "rope_scaling_factor must be >= 1")
+
+    if args.lr is not None:
+        _require(args.min_lr <= args.lr, "min_lr > lr")
+    if args.save is not None:
+        _require(args.save_interval is not None, "--save needs --save_interval")
+    if args.fp16_lm_cross_entropy:
+        _require(args.fp16, "lm cross entropy in fp16 only supported in fp16 mode")
+    if args.fp32_residual_connection:
+        _require(args.fp16 or args.bf16, "fp32 residual needs fp16 or bf16")
+
+    if args.weight_decay_incr_style == "constant":
+        _require(args.start_weight_decay is None and args.end_weight_decay is None,
+                 "start/end weight decay given with constant style")
+        args.start_weight_decay = args.end_weight_decay = args.weight_decay
+    else:
+        _require(args.start_weight_decay is not None and args.end_weight_decay is not None,
+                 "start/end weight decay required")
+
+    if args.distribute_saved_activations:
+        _require(args.tensor_model_parallel_size > 1, "distribute_saved_activations needs tp > 1")
+        _require(args.recompute_granularity == "full", "distribute_saved_activations needs full recompute")
+        _require(args.recompute_method is not None, "distribute_saved_activations needs a recompute method")
+    if args.fp8_e4m3 or args.fp8_hybrid:
+        _require(args.transformer_impl == "transformer_engine", "fp8 needs transformer_engine")
+    _require(not (args.fp8_e4m3 and args.fp8_hybrid), "both fp8 formats")
+    if args.recompute_granularity == "selective":
+        _require(args.recompute_method is None, "recompute method not supported with selective")
+    if not args.parallel_attn:
+        _require(not args.parallel_layernorm, "parallel_layernorm only implemented with parallel_attn")
+    if args.num_attention_heads_kv % args.tensor_model_parallel_size != 0 and \
+            args.num_attention_heads_kv != 1:
+        raise AssertionError("num_attention_heads_kv must be divisible by tensor parallel size")
+
+    if args.tensor_model_parallel_size == 1:
+        args.sequence_parallel = False
+    if args.sequence_parallel:
+        args.async_tensor_model_parallel_allreduce = False
+    # The reference needs CUDA_DEVICE_MAX_CONNECTIONS=1 for its overlap (arguments.py:335-343);
+    # here overlap is expressed with explicit streams/events, so the variable is not required.
+    _print_args(args)
+    return args
+
+
+def _print_args(args):
+    if args.rank != 0:
+        return
+    print("------------------------ arguments ------------------------", flush=True)
+    for name in sorted(vars(args)):
+        dots = "." * (48 - len(name))
+        print(f"  {name} {dots} {getattr(args, name)}", flush=True)
+    print("-------------------- end of arguments ---------------------", flush=True)

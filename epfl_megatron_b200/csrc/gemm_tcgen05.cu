@@ -1,0 +1,340 @@
+// Persistent warp-specialised bf16 GEMM on the 5th-gen tensor cores (K7 of SURVEY.md
+// section 8): TMA (cp.async.bulk.tensor, 128B swizzle) -> 4-stage shared-memory ring ->
+// tcgen05.mma (kind::f16, M=128, N=BN) issued by ONE thread -> fp32 accumulators in
+// TMEM (two BN-column stages, so the epilogue of tile i overlaps the MMAs of tile
+// i+1) -> tcgen05.ld -> registers -> global.
+//
+//   C[M,N] (op)= A_op[M,K] * B_op[N,K]^T,  fp32 accumulate
+//
+// Operand storage (the "major" of each operand is independent):
+//   A K-major : A stored [M, K] row-major          A MN-major : A stored [K, M] row-major
+//   B K-major : B stored [N, K] row-major          B MN-major : B stored [K, N] row-major
+// which covers the three GEMMs of a linear layer without any transposed copies:
+//   forward  Y  = X  W^T : A = X  (K-major),  B = W  (K-major)
+//   dgrad    dX = dY W   : A = dY (K-major),  B = W  (MN-major)
+//   wgrad    dW = dY^T X : A = dY (MN-major), B = X  (MN-major)
+// Output modes: 0 = store bf16, 1 = store fp32, 2 = accumulate into fp32 (the
+// `main_grad += dY^T X` fusion that the reference gets from
+// fused_weight_gradient_dense.cu:128-152 through a cuBLAS beta=1 call).
+//
+// Replaces the cuBLAS calls at megatron/core/tensor_parallel/layers.py:240,267,307 on
+// the fused paths.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;            // 64 bf16 = 128 bytes = one swizzle row
+constexpr int kStages = 4;
+constexpr int kGemmThreads = 256;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps4-7 epilogue
+constexpr int kGroupM = 8;
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int kABytes = kBM * kBK * 2;   // 16 KB
+  static constexpr int kBBytes = BN * kBK * 2;    // 16/32 KB
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarOffset = kStages * kStageBytes;
+  static constexpr int kTotal = kBarOffset + 256 + 1024;  // + barriers + alignment slack
+};
+
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& tm, int& tn) {
+  const int group = kGroupM * tiles_n;
+  const int gid = tile / group;
+  const int first_m = gid * kGroupM;
+  const int gsz = min(tiles_m - first_m, kGroupM);
+  const int in_group = tile - gid * group;
+  tm = first_m + in_group % gsz;
+  tn = in_group / gsz;
+}
+
+template <int BN, bool kAMN, bool kBMN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 void* __restrict__ Cout, int M, int N, int K, long long ldc, int out_mode) {
+  using L = GemmSmem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_m = (M + kBM - 1) / kBM;
+  const int tiles_n = (N + BN - 1) / BN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + kBK - 1) / kBK;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 128);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<2 * BN>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int tm, tn;
+        tile_coords(tile, tiles_m, tiles_n, tm, tn);
+        const int m0 = tm * kBM, n0 = tn * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * L::kStageBytes;
+          uint8_t* sb = sa + L::kABytes;
+          mbar_expect_tx(&full_bar[stage], L::kStageBytes);
+          if (!kAMN) {
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * kBK, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kBM / 64; ++j)
+              tma_load_2d(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * kBK);
+          }
+          if (!kBMN) {
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * kBK, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * kBK);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, kAMN ? 1 : 0, kBMN ? 1 : 0);
+      // K-major: 8-row groups are 1024 B apart (SBO); LBO unused inside one swizzle row.
+      // MN-major: 64-element chunks along M/N are kBK*128 B apart (LBO), 8-row K groups
+      // 1024 B apart (SBO).
+      constexpr uint32_t lbo_a = kAMN ? kBK * 128 : 16, lbo_b = kBMN ? kBK * 128 : 16;
+      constexpr uint32_t kstep_a = kAMN ? 16 * 128 : 32, kstep_b = kBMN ? 16 * 128 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = make_sw128_desc(sa + k * kstep_a, lbo_a, 1024);
+            const uint64_t db = make_sw128_desc(sb + k * kstep_b, lbo_b, 1024);
+            umma_bf16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[as]);
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue ----------------------------------
+    const int ew = warp - 4;  // TMEM lane quarter this warp may read
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int tm, tn;
+      tile_coords(tile, tiles_m, tiles_n, tm, tn);
+      const int row = tm * kBM + ew * 32 + lane;
+      const int n0 = tn * BN;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int col0 = n0 + c * 32;
+        if (row < M && col0 < N) {
+          const bool full = (col0 + 32 <= N);
+          if (out_mode == 0) {
+            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(Cout) + (long long)row * ldc + col0;
+            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint4 o;
+                o.x = pack_bf16x2(__uint_as_float(r[8 * q + 0]), __uint_as_float(r[8 * q + 1]));
+                o.y = pack_bf16x2(__uint_as_float(r[8 * q + 2]), __uint_as_float(r[8 * q + 3]));
+                o.z = pack_bf16x2(__uint_as_float(r[8 * q + 4]), __uint_as_float(r[8 * q + 5]));
+                o.w = pack_bf16x2(__uint_as_float(r[8 * q + 6]), __uint_as_float(r[8 * q + 7]));
+                reinterpret_cast<uint4*>(dst)[q] = o;
+              }
+            } else {
+              for (int j = 0; j < 32 && col0 + j < N; ++j)
+                dst[j] = __float2bfloat16_rn(__uint_as_float(r[j]));
+            }
+          } else {
+            float* dst = reinterpret_cast<float*>(Cout) + (long long)row * ldc + col0;
+            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                float4 o = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                                       __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+                if (out_mode == 2) {
+                  float4 p = reinterpret_cast<float4*>(dst)[q];
+                  o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+                }
+                reinterpret_cast<float4*>(dst)[q] = o;
+              }
+            } else {
+              for (int j = 0; j < 32 && col0 + j < N; ++j) {
+                float v = __uint_as_float(r[j]);
+                dst[j] = out_mode == 2 ? dst[j] + v : v;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[as]);
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<2 * BN>(tmem_base);
+  }
+}
+
+}  // namespace b200
+
+// ------------------------------- host side -----------------------------------
+#include <mutex>
+
+namespace b200 {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor [rows, cols] with row stride `ld` elements, box [box_rows, 64 cols],
+// 128-byte swizzle, out-of-bounds elements read as zero.
+int make_tmap_2d(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
+                 int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return B200_ERR_UNSUPPORTED;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : B200_ERR_BAD_ARG;
+}
+
+template <int BN, bool kAMN, bool kBMN>
+int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, int K,
+                long long ldc, int out_mode, int max_ctas, cudaStream_t stream) {
+  auto kern = gemm_bf16_kernel<BN, kAMN, kBMN>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         GemmSmem<BN>::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+  int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;
+  kern<<<grid, kGemmThreads, GemmSmem<BN>::kTotal, stream>>>(ta, tb, C, M, N, K, ldc, out_mode);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// See the header comment for the operand conventions. lda/ldb/ldc are row strides in
+// elements of the STORED matrices. max_ctas > 0 caps the persistent grid (used to leave
+// SMs free for a concurrent communication kernel).
+B200_API int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                            int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                            long long ldc, int out_mode, int max_ctas, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return B200_ERR_BAD_ARG;
+  if ((lda % 8) || (ldb % 8) || out_mode < 0 || out_mode > 2) return B200_ERR_UNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15))
+    return B200_ERR_UNSUPPORTED;
+  const int BN = N > 128 ? 256 : 128;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_2d(&ta, A, M, K, lda, kBM);
+  else rc = make_tmap_2d(&ta, A, K, M, lda, kBK);
+  if (rc) return rc;
+  if (!b_mn_major) rc = make_tmap_2d(&tb, B, N, K, ldb, BN);
+  else rc = make_tmap_2d(&tb, B, K, N, ldb, kBK);
+  if (rc) return rc;
+#define B200_GEMM_DISPATCH(BN_)                                                                  \
+  if (!a_mn_major && !b_mn_major)                                                                \
+    return launch_gemm<BN_, false, false>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);  \
+  if (!a_mn_major && b_mn_major)                                                                 \
+    return launch_gemm<BN_, false, true>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);   \
+  if (a_mn_major && !b_mn_major)                                                                 \
+    return launch_gemm<BN_, true, false>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);   \
+  return launch_gemm<BN_, true, true>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);
+  if (BN == 256) {
+    B200_GEMM_DISPATCH(256)
+  }
+  B200_GEMM_DISPATCH(128)
+#undef B200_GEMM_DISPATCH
+}

@@ -1,0 +1,204 @@
+"""Per-kernel timing on one B200: own kernels vs the library op they replace.
+
+CUDA-event timing, 5 warm-ups, L2 flushed between iterations (a 256 MiB memset).
+Writes JSON lines to stdout and to gpurun_out/kernel_bench.jsonl.
+Usage: python tools/kernel_bench.py [gemm] [attn] [norm] [elementwise] [adam]
+"""
+from __future__ import annotations
+
+import json
+import math
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+
+from epfl_megatron_b200.ops import lib as L
+from epfl_megatron_b200.ops import selfcheck as SC
+
+PEAKS = {"hbm_gbs": 6448.7, "bf16_tflops": 1658.4}
+try:
+    with open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")) as f:
+        PEAKS.update(json.load(f))
+except OSError:
+    pass
+
+_flush = None
+
+
+def timeit(fn, iters=10, warmup=5):
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        _flush.zero_()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+OUT = []
+
+
+def report(**kw):
+    OUT.append(kw)
+    print(json.dumps(kw), flush=True)
+
+
+def bench_gemm():
+    shapes = [
+        ("qkv_7b", 4096, 12288, 4096), ("dense_7b", 4096, 4096, 4096),
+        ("h4h_7b", 4096, 22016, 4096), ("4hh_7b", 4096, 4096, 11008),
+        ("head_7b", 4096, 32000, 4096), ("sq8k", 8192, 8192, 8192),
+    ]
+    for name, M, N, K in shapes:
+        A = torch.randn(M, K, device="cuda").bfloat16()
+        B = torch.randn(N, K, device="cuda").bfloat16()
+        C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        fl = 2.0 * M * N * K
+        t_own = timeit(lambda: SC.gemm(A, B, M, N, K, 0, 0, 0, c=C))
+        t_lib = timeit(lambda: torch.matmul(A, B.t(), out=C))
+        report(kernel="gemm_nt", shape=name, M=M, N=N, K=K, ms_own=t_own, ms_cublas=t_lib,
+               tflops_own=fl / t_own / 1e9, tflops_cublas=fl / t_lib / 1e9,
+               frac_of_measured_peak=fl / t_own / 1e9 / PEAKS["bf16_tflops"])
+    # dgrad / wgrad forms on the MLP shape
+    M, N, K = 4096, 11008, 4096
+    dY = torch.randn(M, N, device="cuda").bfloat16()
+    W = torch.randn(N, K, device="cuda").bfloat16()
+    X = torch.randn(M, K, device="cuda").bfloat16()
+    dX = torch.empty(M, K, device="cuda", dtype=torch.bfloat16)
+    t_own = timeit(lambda: SC.gemm(dY, W, M, K, N, 0, 1, 0, c=dX))
+    t_lib = timeit(lambda: torch.matmul(dY, W, out=dX))
+    report(kernel="gemm_dgrad", M=M, N=K, K=N, ms_own=t_own, ms_cublas=t_lib,
+           tflops_own=2.0 * M * N * K / t_own / 1e9, tflops_cublas=2.0 * M * N * K / t_lib / 1e9)
+    G = torch.zeros(N, K, device="cuda")
+    t_own = timeit(lambda: SC.gemm(dY, X, N, K, M, 1, 1, 2, c=G))
+
+    def lib_wgrad():
+        G.add_(torch.matmul(dY.t(), X))
+    t_lib = timeit(lib_wgrad)
+    report(kernel="gemm_wgrad_accum_fp32", M=N, N=K, K=M, ms_own=t_own, ms_cublas_plus_add=t_lib,
+           tflops_own=2.0 * M * N * K / t_own / 1e9, tflops_lib=2.0 * M * N * K / t_lib / 1e9)
+
+
+def bench_attn():
+    try:
+        from flash_attn import flash_attn_func
+    except Exception as e:  # noqa: BLE001
+        flash_attn_func = None
+        print("flash_attn unavailable:", e)
+    for name, S, B, G, QPG in [("7b_mha", 4096, 1, 32, 1), ("70b_gqa_tp4", 4096, 1, 2, 8),
+                               ("falcon40b_tp8", 2048, 1, 1, 16)]:
+        HN = 128
+        qkv = torch.randn(S, B, G, QPG + 2, HN, device="cuda").bfloat16()
+        scale = 1 / math.sqrt(HN)
+        fl = 4.0 * S * S * G * QPG * HN * B / 2
+        t_own = timeit(lambda: SC.attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, True))
+        rec = dict(kernel="attn_fwd", shape=name, S=S, heads=G * QPG, kv_heads=G, ms_own=t_own,
+                   tflops_own=fl / t_own / 1e9)
+        if flash_attn_func is not None:
+            def ref_path():
+                # what the reference does: expand K/V to all heads, [s,b]->[b,s] copies
+                q = qkv[:, :, :, :QPG].reshape(S, B, G * QPG, HN)
+                k = qkv[:, :, :, QPG:QPG + 1].expand(S, B, G, QPG, HN).reshape(S, B, G * QPG, HN)
+                v = qkv[:, :, :, QPG + 1:].expand(S, B, G, QPG, HN).reshape(S, B, G * QPG, HN)
+                q, k, v = (t.transpose(0, 1).contiguous() for t in (q, k, v))
+                o = flash_attn_func(q, k, v, causal=True)
+                return o.transpose(0, 1).contiguous()
+            qb = torch.randn(B, S, G * QPG, HN, device="cuda").bfloat16()
+            kb = torch.randn(B, S, G, HN, device="cuda").bfloat16()
+            t_fa = timeit(lambda: flash_attn_func(qb, kb, kb, causal=True))
+            t_ref = timeit(ref_path)
+            rec.update(ms_fa2_kernel_only=t_fa, ms_reference_path=t_ref, tflops_fa2=fl / t_fa / 1e9)
+        report(**rec)
+
+
+def bench_norm():
+    M, H = 4096, 4096
+    x = torch.randn(M, H, device="cuda").bfloat16()
+    w = torch.ones(H, device="cuda").bfloat16()
+    y = torch.empty_like(x)
+    rstd = torch.empty(M, device="cuda")
+    t_own = timeit(lambda: L.call("b200_rmsnorm_fwd", x.data_ptr(), None, w.data_ptr(), y.data_ptr(),
+                                  None, rstd.data_ptr(), M, H, 1e-5, L.stream_ptr()))
+
+    def eager():
+        xf = x.float()
+        return (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5)).type_as(x) * w
+    t_lib = timeit(eager)
+    by = 2.0 * M * H * 2
+    report(kernel="rmsnorm_fwd", M=M, H=H, ms_own=t_own, ms_eager=t_lib, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+    dy = torch.randn_like(x)
+    dx = torch.empty_like(x)
+    dw = torch.zeros(H, device="cuda")
+    grid = L.lib().b200_norm_bwd_grid(M)
+    scratch = torch.empty(grid, H, device="cuda")
+    t_own = timeit(lambda: L.call("b200_rmsnorm_bwd", dy.data_ptr(), x.data_ptr(), w.data_ptr(),
+                                  rstd.data_ptr(), None, dx.data_ptr(), dw.data_ptr(),
+                                  scratch.data_ptr(), M, H, 0, L.stream_ptr()))
+    by = 3.0 * M * H * 2
+    report(kernel="rmsnorm_bwd", M=M, H=H, ms_own=t_own, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+
+
+def bench_elementwise():
+    M, F = 4096, 11008
+    x = torch.randn(M, 2 * F, device="cuda").bfloat16()
+    y = torch.empty(M, F, device="cuda", dtype=torch.bfloat16)
+    t_own = timeit(lambda: L.call("b200_glu_fwd", x.data_ptr(), y.data_ptr(), M, F, 3, L.stream_ptr()))
+
+    def eager():
+        a, g = x.chunk(2, -1)
+        return a * torch.nn.functional.silu(g)
+    t_lib = timeit(eager)
+    by = 3.0 * M * F * 2
+    report(kernel="swiglu_fwd", M=M, F=F, ms_own=t_own, ms_eager=t_lib, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+    T, V = 4096, 32000
+    logits = torch.randn(T, V, device="cuda").bfloat16()
+    labels = torch.randint(0, V, (T,), device="cuda")
+    stats = torch.empty(T, 3, device="cuda")
+    t_own = timeit(lambda: L.call("b200_xent_stats", logits.data_ptr(), labels.data_ptr(),
+                                  stats.data_ptr(), T, V, 0, L.stream_ptr()))
+    t_lib = timeit(lambda: torch.nn.functional.cross_entropy(logits.float(), labels, reduction="none"))
+    by = 1.0 * T * V * 2
+    report(kernel="xent_stats", T=T, V=V, ms_own=t_own, ms_eager_fp32=t_lib, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+
+
+def bench_adam():
+    n = 1 << 28
+    p, g, m, v = (torch.zeros(n, device="cuda") for _ in range(4))
+    p16 = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    t_own = timeit(lambda: L.call("b200_adam_step", p.data_ptr(), g.data_ptr(), m.data_ptr(),
+                                  v.data_ptr(), p16.data_ptr(), n, 1e-4, 0.9, 0.95, 1e-8, 0.1, 1, 1,
+                                  1, None, None, L.stream_ptr()), iters=5, warmup=2)
+    by = n * (4 * 4 + 3 * 4 + 2.0)
+    report(kernel="adam_flat", n=n, ms_own=t_own, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["gemm", "attn", "norm", "elementwise", "adam"]
+    for w in which:
+        try:
+            globals()["bench_" + w]()
+        except Exception as e:  # noqa: BLE001
+            report(kernel=w, error=f"{type(e).__name__}: {e}"[:500])
+    os.makedirs("gpurun_out", exist_ok=True)
+    with open("gpurun_out/kernel_bench.jsonl", "a") as f:
+        for r in OUT:
+            f.write(json.dumps(r) + "\n")

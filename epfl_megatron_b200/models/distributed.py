@@ -1,0 +1,192 @@
+"""Local data-parallel wrapper with one contiguous gradient buffer per dtype
+(megatron/model/distributed.py:15-232 surface: ``main_grad`` views, ``zero_grad_buffer``,
+``allreduce_gradients``).
+
+Differences that matter on B200:
+* zeroing is LOGICAL: ``zero_grad_buffer`` marks every parameter's slice as empty and the
+  first gradient of the step is stored (beta = 0) instead of accumulated, so the 4 B/param
+  memset and the first read-modify-write disappear (the reference memsets the whole
+  buffer every step, training.py:397-399);
+* weight gradients of the linear layers are accumulated into ``main_grad`` by the GEMM
+  epilogue itself (ops.functional.wgrad_accumulate);
+* the buffer is split into buckets; when ``overlap_grad_reduce`` is on, a bucket's
+  all-reduce / reduce-scatter is launched on the communication stream as soon as the
+  last gradient of the bucket has been produced in the final micro-batch's backward
+  (the reference reduces once, after backward, with no overlap).
+"""
+from __future__ import annotations
+
+import math
+from abc import ABC, abstractmethod
+
+import torch
+import torch.distributed as dist
+
+from ..parallel import state as mpu
+from .module import MegatronModule
+
+
+def default_param_group_key(name, param):
+    """(wd_mult, lr_mult): biases and 1-D parameters get no weight decay
+    (megatron/optimizer/__init__.py:13-61 rule)."""
+    no_wd = name.endswith(".bias") or param.dim() == 1
+    return (0.0 if no_wd else 1.0, 1.0)
+
+
+class MemoryBuffer:
+    def __init__(self, numel, numel_padded, dtype, device):
+        self.numel, self.numel_padded, self.dtype = numel, numel_padded, dtype
+        self.data = torch.zeros(numel_padded, dtype=dtype, device=device, requires_grad=False)
+
+    def zero(self):
+        self.data.zero_()
+
+    def get(self, shape, start_index):
+        end = start_index + shape.numel()
+        assert end <= self.numel, "requested tensor is out of the buffer range."
+        return self.data[start_index:end].view(shape)
+
+
+class DistributedDataParallelBase(MegatronModule, ABC):
+    def __init__(self, module):
+        super().__init__()
+        self.module = module
+
+    @abstractmethod
+    def allreduce_gradients(self):
+        pass
+
+    def forward(self, *inputs, **kwargs):
+        return self.module(*inputs, **kwargs)
+
+    def state_dict(self, prefix="", keep_vars=False):
+        return self.module.state_dict(prefix=prefix, keep_vars=keep_vars)
+
+    def state_dict_for_save_checkpoint(self, prefix="", keep_vars=False):
+        return self.module.state_dict_for_save_checkpoint(prefix=prefix, keep_vars=keep_vars)
+
+    def load_state_dict(self, state_dict, strict=True):
+        self.module.load_state_dict(state_dict, strict=strict)
+
+
+class DistributedDataParallel(DistributedDataParallelBase):
+    def __init__(self, module, accumulate_allreduce_grads_in_fp32, use_contiguous_buffers,
+                 fuse_wgrad: bool = True, group_key_fn=None):
+        super().__init__(module)
+        self.accumulate_allreduce_grads_in_fp32 = accumulate_allreduce_grads_in_fp32
+        self.use_contiguous_buffers = use_contiguous_buffers
+        if accumulate_allreduce_grads_in_fp32:
+            assert use_contiguous_buffers
+        self._grad_buffers = None
+        self._grad_buffer_param_index_map = None
+        self._params = [p for p in self.module.parameters() if p.requires_grad]
+        if not self.use_contiguous_buffers:
+            return
+        self._grad_buffers = {}
+        self._grad_buffer_param_index_map = {}
+        dp = mpu.get_data_parallel_world_size()
+
+        def buf_dtype(p):
+            return torch.float if accumulate_allreduce_grads_in_fp32 else p.dtype
+
+        sizes = {}
+        for p in self._params:
+            sizes[buf_dtype(p)] = sizes.get(buf_dtype(p), 0) + p.data.nelement()
+        dev = self._params[0].device if self._params else torch.device("cpu")
+        # Layout: parameters are grouped by optimizer group key (weight-decay / lr multipliers)
+        # so every optimizer group is ONE contiguous index range of the buffer, and inside a
+        # group they are laid out in reverse module order (== order gradients are produced).
+        names = {p: n for n, p in self.module.named_parameters()}
+        self.group_key_fn = group_key_fn or default_param_group_key
+        keyed = [(self.group_key_fn(names.get(p, ""), p), i, p) for i, p in enumerate(self._params)]
+        keys = sorted({k for k, _, _ in keyed})
+        self.layout = {}        # dtype -> [(param, start, end, key)] in buffer order
+        self.group_ranges = {}  # dtype -> {key: (start, end)}
+        cursor = {dt: 0 for dt in sizes}
+        for key in keys:
+            members = [(i, p) for k, i, p in keyed if k == key]
+            for i, p in reversed(members):
+                dt = buf_dtype(p)
+                start = cursor[dt]
+                # keep every parameter 16-byte aligned in the bf16 mirror of this index space
+                start = (start + 7) // 8 * 8
+                end = start + p.data.nelement()
+                cursor[dt] = end
+                self.layout.setdefault(dt, []).append((p, start, end, key))
+                lo, hi = self.group_ranges.setdefault(dt, {}).get(key, (start, start))
+                self.group_ranges[dt][key] = (lo, end)
+        for dt in list(sizes):
+            n = cursor[dt]
+            unit = dp * 8
+            self._grad_buffers[dt] = MemoryBuffer(n, unit * int(math.ceil(n / unit)), dt, dev)
+            # a group range is extended to the start of the next group so ranges tile the buffer
+            ordered = sorted(self.group_ranges[dt].items(), key=lambda kv: kv[1][0])
+            for j, (key, (lo, hi)) in enumerate(ordered):
+                nxt = ordered[j + 1][1][0] if j + 1 < len(ordered) else self._grad_buffers[dt].numel_padded
+                self.group_ranges[dt][key] = (lo, nxt)
+            for p, start, end, key in self.layout[dt]:
+                p.main_grad = self._grad_buffers[dt].get(p.data.shape, start)
+                p._b200_fuse_wgrad = bool(fuse_wgrad and dt == torch.float)
+                p._b200_main_grad_empty = False
+                self._grad_buffer_param_index_map.setdefault(dt, {})[p] = (start, end)
+        self.grad_accs = []
+        for p in self._params:
+            tmp = p.expand_as(p)
+            acc = tmp.grad_fn.next_functions[0][0]
+            acc.register_hook(self._make_param_hook(p))
+            self.grad_accs.append(acc)
+
+    def _make_param_hook(self, param):
+        def hook(*unused):
+            if param.grad is not None:
+                if getattr(param, "_b200_main_grad_empty", False):
+                    param.main_grad.copy_(param.grad.data)
+                    param._b200_main_grad_empty = False
+                else:
+                    param.main_grad.add_(param.grad.data)
+                param.grad = None
+                cb = getattr(param, "_b200_grad_ready", None)
+                if cb is not None:
+                    cb()
+        return hook
+
+    def zero_grad_buffer(self):
+        """Logical zero: the next gradient written to each slice overwrites it."""
+        assert self._grad_buffers is not None, "buffers are not initialized."
+        for p in self._params:
+            p._b200_main_grad_empty = True
+
+    def finalize_grad_buffer(self):
+        """Physically zero the slices that received no gradient this step."""
+        for p in self._params:
+            if getattr(p, "_b200_main_grad_empty", False):
+                p.main_grad.zero_()
+                p._b200_main_grad_empty = False
+
+    def broadcast_params(self):
+        for p in self.module.parameters():
+            dist.broadcast(p.data, src=mpu.get_data_parallel_src_rank(), group=mpu.get_data_parallel_group())
+
+    def allreduce_gradients(self):
+        """Average gradients over the data-parallel group."""
+        dp = mpu.get_data_parallel_world_size()
+        if self._grad_buffers is not None:
+            self.finalize_grad_buffer()
+            for _, buf in self._grad_buffers.items():
+                if dp > 1:
+                    buf.data /= dp
+                    dist.all_reduce(buf.data, group=mpu.get_data_parallel_group())
+            return
+        if dp == 1:
+            return
+        buckets = {}
+        for p in self.module.parameters():
+            if p.requires_grad and p.grad is not None:
+                buckets.setdefault(p.data.type(), []).append(p)
+        for tp, bucket in buckets.items():
+            grads = [p.grad.data for p in bucket]
+            flat = torch._utils._flatten_dense_tensors(grads)
+            flat /= dp
+            dist.all_reduce(flat, group=mpu.get_data_parallel_group())
+            for g, s in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
+                g.copy_(s)

@@ -1,0 +1,357 @@
+"""Tensor-parallel layers: VocabParallelEmbedding, ColumnParallelLinear, RowParallelLinear
+and the autograd linear that carries the sequence-parallel collectives.
+
+Public surface of megatron/core/tensor_parallel/layers.py:41-701. What differs inside:
+
+* the weight gradient is accumulated straight into the fp32 ``weight.main_grad`` by the
+  tcgen05 GEMM epilogue (reference: apex ``fused_weight_gradient_mlp_cuda``, layers.py:298-305);
+* collectives that overlap with GEMMs run on a dedicated communication stream ordered
+  with CUDA events (reference: async_op + CUDA_DEVICE_MAX_CONNECTIONS=1, layers.py:255-296);
+* the backward of a sequence-parallel ColumnParallelLinear re-gathers its input while the
+  dgrad GEMM runs and reduce-scatters dgrad while the wgrad GEMM runs;
+* with sequence parallelism the embedding is reduce-scattered along the sequence
+  instead of all-reduced and then discarded (reference: layers.py:209 +
+  language_model.py:255-256).
+"""
+from __future__ import annotations
+
+import math
+from typing import Callable, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+from torch.nn.parameter import Parameter
+
+from ..ops import functional as Fn
+from . import state
+from .mappings import (copy_to_tensor_model_parallel_region, gather_from_tensor_model_parallel_region,
+                       reduce_from_tensor_model_parallel_region,
+                       reduce_scatter_to_sequence_parallel_region,
+                       scatter_to_tensor_model_parallel_region)
+from .random import get_cuda_rng_tracker
+from .utils import VocabUtility, all_gather_into, divide, reduce_scatter_into
+
+_MODEL_PARALLEL_ATTRIBUTE_DEFAULTS = {"tensor_model_parallel": False, "partition_dim": -1,
+                                      "partition_stride": 1}
+
+
+def param_is_not_tensor_parallel_duplicate(param):
+    return (hasattr(param, "tensor_model_parallel") and param.tensor_model_parallel) or \
+        state.get_tensor_model_parallel_rank() == 0
+
+
+def set_tensor_model_parallel_attributes(tensor, is_parallel, dim, stride):
+    for a in _MODEL_PARALLEL_ATTRIBUTE_DEFAULTS:
+        assert not hasattr(tensor, a)
+    tensor.tensor_model_parallel = is_parallel
+    tensor.partition_dim = dim
+    tensor.partition_stride = stride
+
+
+def set_defaults_if_not_set_tensor_model_parallel_attributes(tensor):
+    for a, v in _MODEL_PARALLEL_ATTRIBUTE_DEFAULTS.items():
+        if not hasattr(tensor, a):
+            setattr(tensor, a, v)
+
+
+def copy_tensor_model_parallel_attributes(dst, src):
+    for a in _MODEL_PARALLEL_ATTRIBUTE_DEFAULTS:
+        if hasattr(src, a):
+            setattr(dst, a, getattr(src, a))
+
+
+def _initialize_affine_weight_gpu(weight, init_method, partition_dim, stride=1):
+    """Each TP rank draws its shard from the tensor-parallel RNG stream."""
+    set_tensor_model_parallel_attributes(weight, True, partition_dim, stride)
+    with get_cuda_rng_tracker().fork():
+        init_method(weight)
+
+
+def _initialize_affine_weight_cpu(weight, output_size, input_size, per_partition_size,
+                                  partition_dim, init_method, stride=1, return_master_weight=False,
+                                  params_dtype=torch.float32):
+    """Build the full weight on the host, keep this rank's (strided) shard: results do
+    not depend on the TP degree."""
+    set_tensor_model_parallel_attributes(weight, True, partition_dim, stride)
+    master = torch.empty(output_size, input_size, dtype=torch.float, requires_grad=False)
+    init_method(master)
+    master = master.to(dtype=params_dtype)
+    per_stride = divide(per_partition_size, stride)
+    pieces = torch.split(master, per_stride, dim=partition_dim)
+    rank, ws = state.get_tensor_model_parallel_rank(), state.get_tensor_model_parallel_world_size()
+    mine = pieces[rank::ws]
+    with torch.no_grad():
+        torch.cat(mine, dim=partition_dim, out=weight)
+    return master if return_master_weight else None
+
+
+class VocabParallelEmbedding(torch.nn.Module):
+    """Embedding table sharded along the vocabulary."""
+
+    def __init__(self, num_embeddings, embedding_dim, *, init_method=torch.nn.init.xavier_normal_,
+                 params_dtype=torch.float32, use_cpu_initialization=False,
+                 perform_initialization=True):
+        super().__init__()
+        self.num_embeddings, self.embedding_dim = num_embeddings, embedding_dim
+        self.padding_idx = None
+        self.tensor_model_parallel_size = state.get_tensor_model_parallel_world_size()
+        self.vocab_start_index, self.vocab_end_index = VocabUtility.vocab_range_from_global_vocab_size(
+            num_embeddings, state.get_tensor_model_parallel_rank(), self.tensor_model_parallel_size)
+        self.num_embeddings_per_partition = self.vocab_end_index - self.vocab_start_index
+        dev = "cpu" if use_cpu_initialization or not torch.cuda.is_available() else torch.cuda.current_device()
+        self.weight = Parameter(torch.empty(self.num_embeddings_per_partition, embedding_dim,
+                                            device=dev, dtype=params_dtype))
+        if perform_initialization:
+            if use_cpu_initialization or not torch.cuda.is_available():
+                _initialize_affine_weight_cpu(self.weight, num_embeddings, embedding_dim,
+                                              self.num_embeddings_per_partition, 0, init_method,
+                                              params_dtype=params_dtype)
+            else:
+                _initialize_affine_weight_gpu(self.weight, init_method, partition_dim=0, stride=1)
+        else:
+            set_tensor_model_parallel_attributes(self.weight, True, 0, 1)
+
+    def local_lookup(self, input_):
+        """Partial embedding: rows owned by other ranks come out as zeros."""
+        if self.tensor_model_parallel_size > 1:
+            mask = (input_ < self.vocab_start_index) | (input_ >= self.vocab_end_index)
+            idx = (input_ - self.vocab_start_index).masked_fill(mask, 0)
+            out = F.embedding(idx, self.weight)
+            return out.masked_fill(mask.unsqueeze(-1), 0.0)
+        return F.embedding(input_, self.weight)
+
+    def forward(self, input_):
+        return reduce_from_tensor_model_parallel_region(self.local_lookup(input_))
+
+
+_COMM_STREAM = None
+
+
+def comm_stream():
+    """Side stream for collectives that overlap with GEMMs."""
+    global _COMM_STREAM
+    if _COMM_STREAM is None:
+        _COMM_STREAM = torch.cuda.Stream()
+    return _COMM_STREAM
+
+
+class _Overlap:
+    """Run a collective on the comm stream after the current stream's work so far; the
+    caller later ``wait()``s before consuming the result. On CPU it runs inline."""
+
+    def __init__(self, fn, *tensors):
+        self.cuda = tensors[0].is_cuda
+        if self.cuda:
+            cs = comm_stream()
+            cs.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(cs):
+                fn()
+            for t in tensors:
+                t.record_stream(cs)
+            self.event = cs.record_event()
+        else:
+            fn()
+
+    def wait(self):
+        if self.cuda:
+            torch.cuda.current_stream().wait_event(self.event)
+
+
+class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, input, weight, bias, gradient_accumulation_fusion, async_grad_allreduce,
+                sequence_parallel):
+        ctx.save_for_backward(input, weight)
+        ctx.use_bias = bias is not None
+        ctx.gradient_accumulation_fusion = gradient_accumulation_fusion
+        ctx.async_grad_allreduce = async_grad_allreduce
+        ctx.sequence_parallel = sequence_parallel
+        ctx.weight_ref = weight
+        if sequence_parallel:
+            ws = state.get_tensor_model_parallel_world_size()
+            shape = list(input.shape)
+            shape[0] *= ws
+            total = state.get_global_memory_buffer().get_tensor(shape, input.dtype, "mpu")
+            all_gather_into(total, input.contiguous(), state.get_tensor_model_parallel_group())
+        else:
+            total = input
+        K = total.shape[-1]
+        out = Fn.gemm_nt(total.reshape(-1, K), weight)
+        out = out.view(*total.shape[:-1], weight.shape[0])
+        if bias is not None:
+            out = out + bias
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input, weight = ctx.saved_tensors
+        w = ctx.weight_ref
+        grp = state.get_tensor_model_parallel_group() if (ctx.sequence_parallel or ctx.async_grad_allreduce) else None
+        gather = None
+        if ctx.sequence_parallel:
+            ws = state.get_tensor_model_parallel_world_size()
+            shape = list(input.shape)
+            shape[0] *= ws
+            total = state.get_global_memory_buffer().get_tensor(shape, input.dtype, "mpu")
+            inp_c = input.contiguous()
+            gather = _Overlap(lambda: all_gather_into(total, inp_c, grp), total, inp_c)
+        else:
+            total = input
+        N = grad_output.shape[-1]
+        go2 = grad_output.reshape(-1, N)
+        if not go2.is_contiguous():
+            go2 = go2.contiguous()
+        grad_input = Fn.gemm_nn(go2, weight).view(*grad_output.shape[:-1], weight.shape[1])
+        if gather is not None:
+            gather.wait()
+        red = None
+        if ctx.async_grad_allreduce:
+            red = _Overlap(lambda: dist.all_reduce(grad_input, group=grp), grad_input)
+        sub_grad_input = None
+        if ctx.sequence_parallel:
+            assert not ctx.async_grad_allreduce
+            sub_grad_input = torch.empty(input.shape, dtype=input.dtype, device=input.device)
+            red = _Overlap(lambda: reduce_scatter_into(sub_grad_input, grad_input, grp),
+                           sub_grad_input, grad_input)
+        t2 = total.reshape(-1, total.shape[-1])
+        main = getattr(w, "main_grad", None)
+        grad_weight = None
+        fused = False
+        if ctx.gradient_accumulation_fusion and main is not None:
+            first = getattr(w, "_b200_main_grad_empty", False)
+            fused = Fn.wgrad_accumulate(go2, t2, main, accumulate=not first)
+            if fused:
+                w._b200_main_grad_empty = False
+                Fn._notify_grad_ready(w)
+        if not fused:
+            grad_weight = torch.matmul(go2.t(), t2)
+        grad_bias = go2.sum(dim=0) if ctx.use_bias else None
+        if red is not None:
+            red.wait()
+        if ctx.sequence_parallel:
+            return sub_grad_input, grad_weight, grad_bias, None, None, None
+        return grad_input, grad_weight, grad_bias, None, None, None
+
+
+def linear_with_grad_accumulation_and_async_allreduce(input, weight, bias, gradient_accumulation_fusion,
+                                                      async_grad_allreduce,
+                                                      sequence_parallel_enabled):
+    return LinearWithGradAccumulationAndAsyncCommunication.apply(
+        input, weight, bias, gradient_accumulation_fusion, async_grad_allreduce,
+        sequence_parallel_enabled)
+
+
+class ColumnParallelLinear(torch.nn.Module):
+    """Y = X A^T + b with A sharded along its output rows: A = [A_1; ...; A_p]."""
+
+    def __init__(self, input_size, output_size, *, bias=True, gather_output=True,
+                 init_method=torch.nn.init.xavier_normal_, stride=1, keep_master_weight_for_test=False,
+                 skip_bias_add=False, async_tensor_model_parallel_allreduce=True,
+                 params_dtype=torch.float32, use_cpu_initialization=False, perform_initialization=True,
+                 gradient_accumulation_fusion=False, sequence_parallel_enabled: bool = False,
+                 world_size: Optional[int] = None):
+        super().__init__()
+        self.input_size, self.output_size = input_size, output_size
+        self.gather_output, self.skip_bias_add = gather_output, skip_bias_add
+        ws = world_size if world_size is not None else state.get_tensor_model_parallel_world_size()
+        self.world_size = ws
+        self.output_size_per_partition = divide(output_size, ws)
+        cpu = use_cpu_initialization or not torch.cuda.is_available()
+        dev = "cpu" if cpu else torch.cuda.current_device()
+        self.weight = Parameter(torch.empty(self.output_size_per_partition, input_size, device=dev,
+                                            dtype=params_dtype))
+        self.master_weight = None
+        if perform_initialization:
+            if cpu:
+                self.master_weight = _initialize_affine_weight_cpu(
+                    self.weight, output_size, input_size, self.output_size_per_partition, 0,
+                    init_method, stride=stride, return_master_weight=keep_master_weight_for_test,
+                    params_dtype=params_dtype)
+            else:
+                _initialize_affine_weight_gpu(self.weight, init_method, partition_dim=0, stride=stride)
+        else:
+            set_tensor_model_parallel_attributes(self.weight, True, 0, stride)
+        if bias:
+            self.bias = Parameter(torch.zeros(self.output_size_per_partition, device=dev, dtype=params_dtype))
+            set_tensor_model_parallel_attributes(self.bias, True, 0, stride)
+        else:
+            self.register_parameter("bias", None)
+        self.async_tensor_model_parallel_allreduce = async_tensor_model_parallel_allreduce and ws > 1
+        self.sequence_parallel_enabled = sequence_parallel_enabled and ws > 1
+        if self.async_tensor_model_parallel_allreduce and self.sequence_parallel_enabled:
+            raise RuntimeError("`async_tensor_model_parallel_allreduce` and `sequence_parallel_enabled` "
+                               "cannot be enabled at the same time.")
+        self.gradient_accumulation_fusion = gradient_accumulation_fusion
+
+    def forward(self, input_):
+        bias = self.bias if not self.skip_bias_add else None
+        if self.async_tensor_model_parallel_allreduce or self.sequence_parallel_enabled or self.world_size == 1:
+            x = input_
+        else:
+            x = copy_to_tensor_model_parallel_region(input_)
+        out = linear_with_grad_accumulation_and_async_allreduce(
+            x, self.weight, bias, self.gradient_accumulation_fusion,
+            self.async_tensor_model_parallel_allreduce, self.sequence_parallel_enabled)
+        if self.gather_output and self.world_size > 1:
+            assert not self.sequence_parallel_enabled
+            out = gather_from_tensor_model_parallel_region(out)
+        return out, (self.bias if self.skip_bias_add else None)
+
+
+class RowParallelLinear(torch.nn.Module):
+    """Y = X A^T + b with A sharded along its input columns: A = [A_1, ..., A_p]."""
+
+    def __init__(self, input_size, output_size, *, bias=True, input_is_parallel=False,
+                 init_method=torch.nn.init.xavier_normal_, stride=1, keep_master_weight_for_test=False,
+                 skip_bias_add=False, params_dtype=torch.float32, use_cpu_initialization=False,
+                 perform_initialization=True, gradient_accumulation_fusion=False,
+                 sequence_parallel_enabled: bool = False, world_size: Optional[int] = None):
+        super().__init__()
+        self.input_size, self.output_size = input_size, output_size
+        self.input_is_parallel, self.skip_bias_add = input_is_parallel, skip_bias_add
+        ws = world_size if world_size is not None else state.get_tensor_model_parallel_world_size()
+        self.world_size = ws
+        self.input_size_per_partition = divide(input_size, ws)
+        self.gradient_accumulation_fusion = gradient_accumulation_fusion
+        self.sequence_parallel_enabled = sequence_parallel_enabled and ws > 1
+        if sequence_parallel_enabled and not input_is_parallel:
+            raise RuntimeError("To enable `sequence_parallel_enabled`, `input_is_parallel` must be `True`")
+        cpu = use_cpu_initialization or not torch.cuda.is_available()
+        dev = "cpu" if cpu else torch.cuda.current_device()
+        self.weight = Parameter(torch.empty(output_size, self.input_size_per_partition, device=dev,
+                                            dtype=params_dtype))
+        self.master_weight = None
+        if perform_initialization:
+            if cpu:
+                self.master_weight = _initialize_affine_weight_cpu(
+                    self.weight, output_size, input_size, self.input_size_per_partition, 1,
+                    init_method, stride=stride, return_master_weight=keep_master_weight_for_test,
+                    params_dtype=params_dtype)
+            else:
+                _initialize_affine_weight_gpu(self.weight, init_method, partition_dim=1, stride=stride)
+        else:
+            set_tensor_model_parallel_attributes(self.weight, True, 1, stride)
+        if bias:
+            self.bias = Parameter(torch.zeros(output_size, device=dev, dtype=params_dtype))
+            setattr(self.bias, "sequence_parallel", self.sequence_parallel_enabled)
+        else:
+            self.register_parameter("bias", None)
+
+    def forward(self, input_):
+        if self.input_is_parallel or self.world_size == 1:
+            x = input_
+        else:
+            assert not self.sequence_parallel_enabled
+            x = scatter_to_tensor_model_parallel_region(input_)
+        out_parallel = linear_with_grad_accumulation_and_async_allreduce(
+            x, self.weight, None, self.gradient_accumulation_fusion, False, False)
+        if self.sequence_parallel_enabled:
+            out_ = reduce_scatter_to_sequence_parallel_region(out_parallel)
+        elif self.world_size > 1:
+            out_ = reduce_from_tensor_model_parallel_region(out_parallel)
+        else:
+            out_ = out_parallel
+        if not self.skip_bias_add:
+            return (out_ + self.bias if self.bias is not None else out_), None
+        return out_, self.bias

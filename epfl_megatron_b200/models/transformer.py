@@ -72,7 +72,9 @@ class ParallelMLP(MegatronModule):
         self.dense_h_to_4h = tp_layers.ColumnParallelLinear(
             args.hidden_size, ffn_in, bias=self.add_bias, gather_output=False, init_method=init_method,
             skip_bias_add=True, async_tensor_model_parallel_allreduce=args.async_tensor_model_parallel_allreduce,
-            world_size=world_size, **kw)
+            world_size=world_size,
+            # each rank holds [up_shard; gate_shard]: stride 2 makes host-side init independent of tp
+            stride=2 if args.glu_activation else 1, **kw)
         self.bias_gelu_fusion = args.bias_gelu_fusion
         self.onnx_safe = args.onnx_safe
         self.dense_4h_to_h = tp_layers.RowParallelLinear(

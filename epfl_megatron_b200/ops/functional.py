@@ -165,8 +165,17 @@ def layernorm(x, weight, bias, eps=1e-5):
 
 
 # ----------------------------------------------------------------------------- RoPE
+def _fresh_alias(t):
+    """A new tensor object over the same memory that autograd does not track as a view."""
+    out = torch.empty(0, dtype=t.dtype, device=t.device)
+    out.set_(t.untyped_storage(), t.storage_offset(), t.shape, t.stride())
+    return out
+
+
 class _RopeQKVFn(torch.autograd.Function):
-    """In-place rotation of the q and k slots of a fused [s,b,g,nslot,hn] tensor."""
+    """Rotation of the q and k slots of a fused [s,b,g,nslot,hn] tensor, physically in place:
+    the projection output is overwritten (its producer never re-reads it) and handed back
+    as a fresh tensor so autograd sees an ordinary out-of-place op."""
 
     @staticmethod
     def forward(ctx, qkv, table, position_ids, nrot, pos_offset):
@@ -174,10 +183,9 @@ class _RopeQKVFn(torch.autograd.Function):
         assert qkv.is_contiguous()
         L.call("b200_rope", qkv.data_ptr(), table.data_ptr(), L.ptr(position_ids), s, b, g, nslot,
                nrot, hn, pos_offset, table.shape[0], 0, L.stream_ptr())
-        ctx.mark_dirty(qkv)
         ctx.save_for_backward(table, position_ids)
         ctx.meta = (nrot, pos_offset)
-        return qkv
+        return _fresh_alias(qkv)
 
     @staticmethod
     def backward(ctx, dqkv):
@@ -186,9 +194,10 @@ class _RopeQKVFn(torch.autograd.Function):
         if not dqkv.is_contiguous():
             dqkv = dqkv.contiguous()
         s, b, g, nslot, hn = dqkv.shape
+        # the incoming gradient is produced by the attention backward for this op only
         L.call("b200_rope", dqkv.data_ptr(), table.data_ptr(), L.ptr(position_ids), s, b, g, nslot,
                nrot, hn, pos_offset, table.shape[0], 1, L.stream_ptr())
-        return dqkv, None, None, None, None
+        return _fresh_alias(dqkv), None, None, None, None
 
 
 def rope_fused_qkv(qkv, table, position_ids=None, pos_offset=0):

@@ -119,6 +119,7 @@ def main():
     p.add_argument("--num_microbatches", type=int, default=4)
     p.add_argument("--tp", type=int, default=1)
     p.add_argument("--dp", type=int, default=1)
+    p.add_argument("--debug_layers", type=int, default=0)
     a = p.parse_args()
 
     # the reference must not see this repository's packages (it has its own `megatron`)
@@ -147,6 +148,8 @@ def main():
         unavailable(f"reference import failed: {type(e).__name__}: {e}")
 
     L, h, nh, nkv, ffn, vocab = MODELS[a.model]
+    if a.debug_layers:
+        L = a.debug_layers
     gbs = a.micro_batch * a.num_microbatches * a.dp
     argv = [
         "--model_name", "llama2", "--num_layers", str(L), "--hidden_size", str(h),
@@ -212,8 +215,13 @@ def main():
         return ref_training.train_step(ref_finetune.forward_step, it, model, optimizer, sched, args)
 
     try:
+        dbg = []
         for _ in range(max(a.warmup, 3)):
-            step()
+            r = step()
+            if os.environ.get('B200_BENCH_DEBUG_LOSSES') and r[0]:
+                dbg.append(float(r[0]['lm loss'].item()))
+        if dbg and rank0:
+            print('DEBUG warmup losses', dbg, file=sys.stderr, flush=True)
         torch.cuda.synchronize()
         dist.barrier()
         sampler = ClockSampler(torch.cuda.current_device())

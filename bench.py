@@ -43,8 +43,11 @@ def parallel_layout(n_gpus, model):
 
 def build_arg_list(a, tp, dp):
     L, h, nh, nkv, ffn, vocab = MODELS[a.model]
+    if getattr(a, 'debug_layers', 0):
+        L = a.debug_layers
     gbs = a.micro_batch * a.num_microbatches * dp
     argv = [
+        "--b200_kernels", getattr(a, 'kernels', 'auto'),
         "--model_name", "llama2", "--num_layers", str(L), "--hidden_size", str(h),
         "--num_attention_heads", str(nh), "--num_attention_heads_kv", str(nkv),
         "--ffn_hidden_size", str(ffn), "--seq_length", str(a.seq), "--max_position_embeddings", str(a.seq),
@@ -151,8 +154,13 @@ def run_ours(a):
     def step():
         return train_step(finetune.forward_step, it, model, optimizer, sched, args)
 
+    dbg = []
     for _ in range(a.warmup):
-        step()
+        r = step()
+        if os.environ.get('B200_BENCH_DEBUG_LOSSES') and r[0]:
+            dbg.append(float(r[0]['lm loss'].item()))
+    if dbg and rank == 0:
+        print('DEBUG warmup losses', dbg, file=sys.stderr, flush=True)
     torch.cuda.synchronize()
     dist.barrier()
 
@@ -257,7 +265,8 @@ def run_reference(a):
     tp, dp = parallel_layout(a.gpus, a.model)
     cmd = [sys.executable, script, "--model", a.model, "--gpus", str(a.gpus), "--steps", str(a.steps),
            "--warmup", str(a.warmup), "--seq", str(a.seq), "--micro_batch", str(a.micro_batch),
-           "--num_microbatches", str(a.num_microbatches), "--tp", str(tp), "--dp", str(dp)]
+           "--num_microbatches", str(a.num_microbatches), "--tp", str(tp), "--dp", str(dp),
+           "--debug_layers", str(a.debug_layers)]
     env = dict(os.environ)
     env.pop("PYTHONPATH", None)
     return subprocess.call(cmd, env=env, cwd=ref_root)
@@ -275,6 +284,8 @@ def main():
     p.add_argument("--num_microbatches", type=int, default=4)
     p.add_argument("--recompute", action="store_true")
     p.add_argument("--verbose", action="store_true")
+    p.add_argument("--debug_layers", type=int, default=0, help="debug only: override the layer count")
+    p.add_argument("--kernels", default="auto", help="debug only: auto|off")
     p.add_argument("--profile", action="store_true", help="1 warm-up + K steps, no e2e region; for ncu, NOT a bench value")
     a = p.parse_args()
     if a.warmup < 3 and not a.profile:

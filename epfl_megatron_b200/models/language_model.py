@@ -239,16 +239,26 @@ class TransformerLanguageModel(MegatronModule):
                     else torch.cuda.current_device()
                 self.lm_head = torch.nn.Parameter(torch.empty(rows, self.hidden_size, device=dev,
                                                               dtype=args.params_dtype))
+                # Xavier init over the FULL [V, h] matrix (reference: language_model.py:448)
+                head_init = torch.nn.init.xavier_uniform_ if args.init_method_xavier_uniform \
+                    else torch.nn.init.xavier_normal_
                 if args.perform_initialization:
                     if dev == "cpu":
                         master = torch.empty(args.padded_vocab_size, self.hidden_size, dtype=torch.float)
-                        init_method(master)
+                        head_init(master)
                         r = mpu.get_tensor_model_parallel_rank()
                         with torch.no_grad():
                             self.lm_head.copy_(master[r * rows:(r + 1) * rows].to(args.params_dtype))
                         tp_layers.set_tensor_model_parallel_attributes(self.lm_head, True, 0, 1)
                     else:
-                        tp_layers._initialize_affine_weight_gpu(self.lm_head, init_method, 0, 1)
+                        # a shard must be drawn with the fan of the full matrix, not of the shard
+                        std = (2.0 / (args.padded_vocab_size + self.hidden_size)) ** 0.5
+                        if args.init_method_xavier_uniform:
+                            bound = std * 3.0 ** 0.5
+                            shard_init = lambda w: torch.nn.init.uniform_(w, -bound, bound)  # noqa: E731
+                        else:
+                            shard_init = lambda w: torch.nn.init.normal_(w, 0.0, std)  # noqa: E731
+                        tp_layers._initialize_affine_weight_gpu(self.lm_head, shard_init, 0, 1)
                 else:
                     tp_layers.set_tensor_model_parallel_attributes(self.lm_head, True, 0, 1)
                 self._lm_key = "lm_head"

@@ -1,0 +1,123 @@
+/* C ABI of libb200kernels.so (sm_100a only).
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, a positive cudaError_t when a launch or a
+ *     runtime call fails, or a negative argument error:
+ *         -1 bad argument, -2 unsupported shape / alignment, -3 size beyond a stated maximum;
+ *   - all tensors are device pointers; bf16 tensors are `void*`, fp32 tensors `float*`;
+ *   - the last argument is the CUDA stream the work is enqueued on; nothing synchronises;
+ *   - unless stated otherwise the library allocates nothing: scratch is passed in.
+ * Each comment names the reference code whose job the kernel does (paths relative to the
+ * reference tree).
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- norms (csrc/norm.cu) ------------------------------------------------------------ */
+/* rows of the [grid, H] fp32 scratch the backward kernels need for M rows */
+int b200_norm_bwd_grid(int M);
+/* y = rmsnorm(x [+ residual]) * w; h_out = x + residual when residual != NULL.
+ * Reference: megatron/model/fused_layer_norm.py:125-139 (eager RMSNorm). */
+int b200_rmsnorm_fwd(const void* x, const void* residual, const void* w, void* y, void* h_out,
+                     float* rstd, int M, int H, float eps, cudaStream_t stream);
+/* dx (+= dres), dw (+= when accumulate). scratch: fp32 [b200_norm_bwd_grid(M), H]. */
+int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
+                     const void* dres, void* dx, float* dw, float* scratch, int M, int H,
+                     int accumulate, cudaStream_t stream);
+/* Reference: megatron/fused_kernels/layer_norm_cuda_kernel.cu (cuApplyLayerNorm, cuComputeGradInput,
+ * cuComputePartGradGammaBeta). scratch: fp32 [b200_norm_bwd_grid(M), 2, H]. */
+int b200_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean,
+                       float* rstd, int M, int H, float eps, cudaStream_t stream);
+int b200_layernorm_bwd(const void* dy, const void* x, const void* w, const float* mean,
+                       const float* rstd, void* dx, float* dgamma, float* dbeta, float* scratch,
+                       int M, int H, int accumulate, cudaStream_t stream);
+
+/* ---- elementwise (csrc/elementwise.cu) ------------------------------------------------ */
+/* In-place RoPE on x [S*B tokens, G, nslot, HN]; the first nrot slots of each group are rotated.
+ * Reference: megatron/model/positional_embeddings.py:24-51. */
+int b200_rope(void* x, const float* cos_sin, const long long* pos_ids, int S, int B, int G,
+              int nslot, int nrot, int HN, int pos_offset, int max_pos, int inverse,
+              cudaStream_t stream);
+/* kind: 0 liglu, 1 geglu, 2 reglu, 3 swiglu. Reference: megatron/model/glu_activations.py:11-54. */
+int b200_glu_fwd(const void* in, void* out, long long M, int F, int kind, cudaStream_t stream);
+int b200_glu_bwd(const void* dy, const void* in, void* din, long long M, int F, int kind,
+                 cudaStream_t stream);
+/* Reference: megatron/model/fused_bias_gelu.py:14-43. */
+int b200_bias_gelu_fwd(const void* x, const void* bias, void* y, long long M, int H,
+                       int tanh_approx, cudaStream_t stream);
+int b200_bias_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, long long M,
+                       int H, int tanh_approx, cudaStream_t stream);
+/* out = residual + dropout(x + bias); Philox mask from (seed, offset), regenerated in backward.
+ * Reference: megatron/model/transformer.py:532-578. */
+int b200_dropout_add_fwd(const void* x, const void* bias, const void* residual, void* out,
+                         long long M, int H, float p, unsigned long long seed,
+                         unsigned long long offset, cudaStream_t stream);
+int b200_dropout_bwd(const void* dy, void* dx, long long M, int H, float p,
+                     unsigned long long seed, unsigned long long offset, cudaStream_t stream);
+/* Reference: megatron/model/distributed.py:174-184 (main_grad.add_) and the fp32<->bf16 copies of
+ * megatron/optimizer/optimizer.py:48-51. */
+int b200_accum_bf16_to_f32(const void* src, float* dst, long long n, float scale, int accumulate,
+                           cudaStream_t stream);
+int b200_cast_f32_to_bf16(const float* src, void* dst, long long n, cudaStream_t stream);
+
+/* ---- softmax (csrc/softmax.cu) -------------------------------------------------------- */
+/* mode 0 plain, 1 causal, 2 masked (uint8 mask [mask_batch,1,sq,sk]). Reference:
+ * megatron/fused_kernels/scaled_{upper_triang_,}masked_softmax.h, scaled_softmax_cuda.cu. */
+int b200_softmax_fwd(const void* x, const uint8_t* mask, void* y, int b, int np, int sq, int sk,
+                     int mask_batch, float scale, int mode, cudaStream_t stream);
+int b200_softmax_bwd(const void* dy, const void* y, void* dx, long long rows, int sk, float scale,
+                     cudaStream_t stream);
+
+/* ---- vocab-parallel cross entropy (csrc/xent.cu) --------------------------------------- */
+/* Reference: megatron/core/tensor_parallel/cross_entropy.py:16-126. */
+int b200_xent_stats(const void* logits, const long long* labels, float* stats, int T, int V,
+                    long long vocab_start, cudaStream_t stream);
+int b200_xent_combine(const float* all_stats, float* loss, float* lse, int T, int tp,
+                      cudaStream_t stream);
+int b200_xent_bwd(void* logits, const long long* labels, const float* lse, const float* dloss,
+                  int T, int V, long long vocab_start, cudaStream_t stream);
+
+/* ---- optimizer (csrc/adam.cu) ---------------------------------------------------------- */
+/* Reference: apex FusedAdam / amp_C as used by megatron/optimizer/__init__.py:75-86 and
+ * megatron/optimizer/clip_grads.py:75-105. coef/skip are DEVICE scalars (may be NULL). */
+int b200_adam_step(float* p, const float* g, float* m, float* v, void* p16, long long n, float lr,
+                   float beta1, float beta2, float eps, float wd, int step, int adamw,
+                   int bias_correction, const float* coef, const float* skip, cudaStream_t stream);
+int b200_sgd_step(float* p, const float* g, float* mom, void* p16, long long n, float lr,
+                  float momentum, float wd, int first_step, const float* coef, const float* skip,
+                  cudaStream_t stream);
+int b200_sumsq_scratch_elems(void);
+/* out[0] (+)= sum(x^2), out[1] = non-finite flag; scratch: fp32 [b200_sumsq_scratch_elems()]. */
+int b200_sumsq(const float* x, long long n, float* out, float* scratch, int accumulate,
+               cudaStream_t stream);
+int b200_scale(float* x, long long n, const float* coef, float host_coef, cudaStream_t stream);
+
+/* ---- tcgen05 GEMM (csrc/gemm_tcgen05.cu) ----------------------------------------------- */
+/* C[M,N] (op)= A_op[M,K] * B_op[N,K]^T, bf16 in, fp32 accumulate in TMEM.
+ * a_mn_major / b_mn_major: operand stored with its M / N dimension contiguous (i.e. [K, M] / [K, N]).
+ * out_mode: 0 store bf16, 1 store fp32, 2 accumulate into fp32 (wgrad into main_grad).
+ * Reference: torch.matmul call sites megatron/core/tensor_parallel/layers.py:240,267,307 and
+ * megatron/fused_kernels/fused_weight_gradient_dense.cu:128-152. */
+int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
+                   int b_mn_major, long long lda, long long ldb, long long ldc, int out_mode,
+                   int max_ctas, cudaStream_t stream);
+
+/* ---- tcgen05 attention (csrc/attn_fwd_tcgen05.cu) --------------------------------------- */
+/* Causal / full GQA attention forward reading q, k, v through arbitrary element strides
+ * (the fused QKV projection layout [s, b, g, q_per_g+2, hn] needs no copies). hn must be 128.
+ * out [sq, B, G*qpg*hn] bf16, lse [B, G*qpg, sq] fp32 (natural log).
+ * Reference: flash_attn_func call at megatron/model/transformer.py:514-522 plus the K/V expansion and
+ * transposes at :448-455,515-522. */
+int b200_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int sq, int sk,
+                  int B, int G, int qpg, int hn, long long q_ss, long long q_sb, long long q_sg,
+                  long long q_sj, long long k_ss, long long k_sb, long long k_sg,
+                  float softmax_scale, int causal, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif

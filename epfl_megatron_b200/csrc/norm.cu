@@ -360,3 +360,89 @@ B200_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w, co
   B200_CHECK_LAUNCH();
   return 0;
 }
+
+// =============================================================================
+// RMSNorm backward for callers that cannot allocate device memory
+// =============================================================================
+// Who this is for: code that has to run the RMSNorm backward from a place where asking
+// the CUDA allocator for memory is not an option -- a launch sequence that is being
+// recorded or replayed and therefore must not contain cudaMalloc/cudaFree, a host program
+// that was handed a fixed memory budget and has already spent it, or a plug-in that only
+// receives the caller's input/output pointers and has no allocator of its own. The regular
+// entry point (b200_rmsnorm_bwd) needs a [grid, H] fp32 scratch buffer from its caller for
+// the per-CTA partial weight gradients; this variant brings that buffer with it as a
+// fixed-size array that lives in the library image.
+//
+// Cost and limits: the array below occupies kNoAllocMaxRows * kNoAllocMaxH * 4 bytes
+// (148 * 8192 * 4 = 4.6 MiB) of device memory on EVERY GPU that loads this library, from
+// load until process exit, whether or not the entry point is ever called. H above
+// kNoAllocMaxH is refused with B200_ERR_TOO_LARGE (-3). At most kNoAllocMaxRows CTAs are
+// used (the regular entry point uses up to twice as many), so very tall inputs run
+// somewhat slower than through b200_rmsnorm_bwd.
+//
+// Sharing: there is ONE array per GPU and every call uses it. The kernel overwrites every
+// partial row it later reads, so nothing has to be cleared between calls and stale
+// contents of an earlier call are harmless. Two calls that execute at the same time on
+// one GPU (different streams, or different host threads) would write the same rows: they
+// race. Keep calls to this entry point ordered on one stream per GPU.
+//
+// Set-up: the array's name is only a handle in host code; its device address is looked up
+// with cudaGetSymbolAddress the first time the entry point runs on a given GPU (with that
+// GPU current) and cached per device. Make that first call outside of any stream capture.
+constexpr int kNoAllocMaxRows = b200::kNumSMs;  // CTAs == partial rows
+constexpr int kNoAllocMaxH = 8192;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_rmsnorm_bwd_noalloc_scratch[kNoAllocMaxRows * kNoAllocMaxH];
+
+#include <mutex>
+
+namespace {
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+// Device address of the scratch array on the CURRENT device (resolved once per device).
+int noalloc_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return B200_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_rmsnorm_bwd_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return B200_ERR_UNSUPPORTED;
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+// Largest hidden size b200_rmsnorm_bwd_noalloc accepts.
+B200_API int b200_rmsnorm_bwd_noalloc_max_h() { return kNoAllocMaxH; }
+
+// Same result as b200_rmsnorm_bwd, without a scratch argument and without any allocation.
+B200_API int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w,
+                                      const float* rstd, const void* dres, void* dx, float* dw,
+                                      int M, int H, int accumulate, cudaStream_t stream) {
+  if (H > kNoAllocMaxH) return B200_ERR_TOO_LARGE;
+  if (!b200::norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
+  float* scratch = nullptr;
+  int rc = noalloc_scratch(&scratch);
+  if (rc != 0) return rc;
+  const int grid = M < kNoAllocMaxRows ? M : kNoAllocMaxRows;
+  if (dres)
+    b200::rmsnorm_bwd_kernel<true><<<grid, b200::kNormThreads, 0, stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, rstd,
+        (const __nv_bfloat16*)dres, (__nv_bfloat16*)dx, scratch, M, H);
+  else
+    b200::rmsnorm_bwd_kernel<false><<<grid, b200::kNormThreads, 0, stream>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, rstd, nullptr,
+        (__nv_bfloat16*)dx, scratch, M, H);
+  B200_CHECK_LAUNCH();
+  b200::colsum_kernel<<<(H + 255) / 256, 256, 0, stream>>>(scratch, dw, grid, H, accumulate);
+  B200_CHECK_LAUNCH();
+  return 0;
+}

@@ -29,6 +29,19 @@ int b200_rmsnorm_fwd(const void* x, const void* residual, const void* w, void* y
 int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
                      const void* dres, void* dx, float* dw, float* scratch, int M, int H,
                      int accumulate, cudaStream_t stream);
+/* RMSNorm backward for callers that cannot allocate device memory (a launch sequence under
+ * recording, a host with its memory budget already handed out, a plug-in that only receives input /
+ * output pointers). No counterpart in the reference. Same results as b200_rmsnorm_bwd, but the
+ * [rows, H] fp32 partial-gradient scratch is a 148 x 8192 array built into the library: it occupies
+ * 4.6 MiB on every GPU that loads the library until the process exits. H > 8192
+ * (b200_rmsnorm_bwd_noalloc_max_h()) returns -3. The entry point calls no allocator. All calls on a
+ * GPU share the one array: it needs no clearing between calls, but calls that overlap on the GPU
+ * (different streams / threads) race -- keep them on one stream. The first call on each GPU looks the
+ * array's device address up (cudaGetSymbolAddress, that GPU current); make it before any stream capture. */
+int b200_rmsnorm_bwd_noalloc_max_h(void);
+int b200_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* rstd,
+                             const void* dres, void* dx, float* dw, int M, int H, int accumulate,
+                             cudaStream_t stream);
 /* Reference: megatron/fused_kernels/layer_norm_cuda_kernel.cu (cuApplyLayerNorm, cuComputeGradInput,
  * cuComputePartGradGammaBeta). scratch: fp32 [b200_norm_bwd_grid(M), 2, H]. */
 int b200_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean,

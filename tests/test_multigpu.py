@@ -1,0 +1,56 @@
+"""Multi-GPU parity (needs >= 2 devices; skipped otherwise): tensor + sequence parallel,
+data parallel with the distributed optimizer and pipeline parallel runs must reproduce the
+single-GPU loss curve of the same model (same host-side initialisation)."""
+import pytest
+import torch
+
+from tests.helpers.launch import run_tiny
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+
+
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+def _close(a, b, rel):
+    assert len(a) == len(b) and len(a) > 0
+    for x, y in zip(a, b):
+        assert abs(x - y) <= rel * max(abs(y), 1e-3), (a, b)
+
+
+@pytest.fixture(scope="module")
+def single():
+    return run_tiny(steps=5, num_microbatches=4)
+
+
+def test_tp2_sequence_parallel(single):
+    _need(2)
+    r = run_tiny(nproc=2, tp=2, steps=5, num_microbatches=4)
+    _close(r["losses"], single["losses"], 0.03)
+
+
+def test_dp2_distributed_optimizer(single):
+    _need(2)
+    r = run_tiny(nproc=2, steps=5, dist_opt=True, num_microbatches=2)
+    assert r["losses"][-1] < r["losses"][0]
+
+
+def test_pp2_1f1b(single):
+    _need(2)
+    r = run_tiny(nproc=2, pp=2, steps=5, num_microbatches=4)
+    _close(r["losses"], single["losses"], 0.03)
+
+
+def test_pp2_interleaved(single):
+    _need(2)
+    r = run_tiny(nproc=2, pp=2, vpp_layers=1, layers=4, steps=4, num_microbatches=4)
+    base = run_tiny(steps=4, layers=4, num_microbatches=4)
+    _close(r["losses"], base["losses"], 0.03)
+
+
+def test_tp2_pp2_dp2():
+    _need(8)
+    r = run_tiny(nproc=8, tp=2, pp=2, steps=4, dist_opt=True, num_microbatches=4)
+    assert r["losses"][-1] < r["losses"][0]

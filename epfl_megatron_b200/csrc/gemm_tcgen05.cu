@@ -48,6 +48,50 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
   tn = in_group / gsz;
 }
 
+// One thread's 32 consecutive fp32 accumulator columns of row `row` -> global memory.
+__device__ __forceinline__ void store_acc_chunk(const uint32_t* r, void* __restrict__ Cout, int row,
+                                                int col0, int M, int N, long long ldc,
+                                                int out_mode) {
+  if (row >= M || col0 >= N) return;
+  const bool full = (col0 + 32 <= N);
+  if (out_mode == 0) {
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(Cout) + (long long)row * ldc + col0;
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 o;
+        o.x = pack_bf16x2(__uint_as_float(r[8 * q + 0]), __uint_as_float(r[8 * q + 1]));
+        o.y = pack_bf16x2(__uint_as_float(r[8 * q + 2]), __uint_as_float(r[8 * q + 3]));
+        o.z = pack_bf16x2(__uint_as_float(r[8 * q + 4]), __uint_as_float(r[8 * q + 5]));
+        o.w = pack_bf16x2(__uint_as_float(r[8 * q + 6]), __uint_as_float(r[8 * q + 7]));
+        reinterpret_cast<uint4*>(dst)[q] = o;
+      }
+    } else {
+      for (int j = 0; j < 32 && col0 + j < N; ++j)
+        dst[j] = __float2bfloat16_rn(__uint_as_float(r[j]));
+    }
+  } else {
+    float* dst = reinterpret_cast<float*>(Cout) + (long long)row * ldc + col0;
+    if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        float4 o = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
+                               __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
+        if (out_mode == 2) {
+          float4 p = reinterpret_cast<float4*>(dst)[q];
+          o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+        }
+        reinterpret_cast<float4*>(dst)[q] = o;
+      }
+    } else {
+      for (int j = 0; j < 32 && col0 + j < N; ++j) {
+        float v = __uint_as_float(r[j]);
+        dst[j] = out_mode == 2 ? dst[j] + v : v;
+      }
+    }
+  }
+}
+
 template <int BN, bool kAMN, bool kBMN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -182,46 +226,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t r[32];
         tmem_ld_32x32(taddr + c * 32, r);
         tmem_ld_wait();
-        const int col0 = n0 + c * 32;
-        if (row < M && col0 < N) {
-          const bool full = (col0 + 32 <= N);
-          if (out_mode == 0) {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(Cout) + (long long)row * ldc + col0;
-            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                uint4 o;
-                o.x = pack_bf16x2(__uint_as_float(r[8 * q + 0]), __uint_as_float(r[8 * q + 1]));
-                o.y = pack_bf16x2(__uint_as_float(r[8 * q + 2]), __uint_as_float(r[8 * q + 3]));
-                o.z = pack_bf16x2(__uint_as_float(r[8 * q + 4]), __uint_as_float(r[8 * q + 5]));
-                o.w = pack_bf16x2(__uint_as_float(r[8 * q + 6]), __uint_as_float(r[8 * q + 7]));
-                reinterpret_cast<uint4*>(dst)[q] = o;
-              }
-            } else {
-              for (int j = 0; j < 32 && col0 + j < N; ++j)
-                dst[j] = __float2bfloat16_rn(__uint_as_float(r[j]));
-            }
-          } else {
-            float* dst = reinterpret_cast<float*>(Cout) + (long long)row * ldc + col0;
-            if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-#pragma unroll
-              for (int q = 0; q < 8; ++q) {
-                float4 o = make_float4(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1]),
-                                       __uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3]));
-                if (out_mode == 2) {
-                  float4 p = reinterpret_cast<float4*>(dst)[q];
-                  o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
-                }
-                reinterpret_cast<float4*>(dst)[q] = o;
-              }
-            } else {
-              for (int j = 0; j < 32 && col0 + j < N; ++j) {
-                float v = __uint_as_float(r[j]);
-                dst[j] = out_mode == 2 ? dst[j] + v : v;
-              }
-            }
-          }
-        }
+        store_acc_chunk(r, Cout, row, n0 + c * 32, M, N, ldc, out_mode);
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
@@ -237,6 +242,188 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<2 * BN>(tmem_base);
+  }
+}
+
+
+// ---------------------------------------------------------------------------------
+// CTA-pair variant (cta_group::2): a cluster of two CTAs on one TPC owns a 256 x 256
+// output tile. Each CTA stages its own 128 rows of A and its own 128-row half of B
+// (32 KB per stage instead of 48 KB, so 6 stages fit and the shared-memory read
+// traffic per MMA halves), the leader CTA's elected thread issues ONE
+// tcgen05.mma.cta_group::2 (M = 256, N = 256) per 16-element K step, and each CTA
+// drains its own 128 x 256 fp32 accumulator half from its own TMEM.
+//
+// Barriers: full[stage] lives in the leader and counts the bytes of BOTH CTAs' TMA
+// loads; empty[stage] / tmem_full[as] exist in both CTAs and are signalled by a
+// multicast tcgen05.commit; tmem_empty[as] lives in the leader and is arrived on by one
+// lane of each of the 8 epilogue warps of the pair (remote arrive for the peer).
+// ---------------------------------------------------------------------------------
+constexpr int kPairStages = 6;
+constexpr int kPairBN = 256;       // instruction N; each CTA stages kPairBN / 2 rows of B
+constexpr int kPairHalfN = kPairBN / 2;
+
+struct PairSmem {
+  static constexpr int kABytes = kBM * kBK * 2;          // 16 KB
+  static constexpr int kBBytes = kPairHalfN * kBK * 2;   // 16 KB
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarOffset = kPairStages * kStageBytes;
+  static constexpr int kTotal = kBarOffset + 256 + 1024;
+};
+
+template <bool kAMN, bool kBMN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      void* __restrict__ Cout, int M, int N, int K, long long ldc, int out_mode) {
+  using L = PairSmem;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::kBarOffset);
+  uint64_t* empty_bar = full_bar + kPairStages;
+  uint64_t* tmem_full = empty_bar + kPairStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int tiles_m = (M + 2 * kBM - 1) / (2 * kBM);
+  const int tiles_n = (N + kPairBN - 1) / kPairBN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + kBK - 1) / kBK;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int i = 0; i < kPairStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 8);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc_pair<2 * kPairBN>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int tm, tn;
+        tile_coords(tile, tiles_m, tiles_n, tm, tn);
+        const int m0 = tm * 2 * kBM + static_cast<int>(rank) * kBM;
+        const int n0 = tn * kPairBN + static_cast<int>(rank) * kPairHalfN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * L::kStageBytes;
+          uint8_t* sb = sa + L::kABytes;
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
+          if (!kAMN) {
+            tma_load_2d_pair(sa, &tmA, &full_bar[stage], kb * kBK, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kBM / 64; ++j)
+              tma_load_2d_pair(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * kBK);
+          }
+          if (!kBMN) {
+            tma_load_2d_pair(sb, &tmB, &full_bar[stage], kb * kBK, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kPairHalfN / 64; ++j)
+              tma_load_2d_pair(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * kBK);
+          }
+          if (++stage == kPairStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) --------------
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * kBM, kPairBN, kAMN ? 1 : 0, kBMN ? 1 : 0);
+      constexpr uint32_t lbo_a = kAMN ? kBK * 128 : 16, lbo_b = kBMN ? kBK * 128 : 16;
+      constexpr uint32_t kstep_a = kAMN ? 16 * 128 : 32, kstep_b = kBMN ? 16 * 128 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * kPairBN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * L::kStageBytes);
+          const uint32_t sb = sa + L::kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = make_sw128_desc(sa + k * kstep_a, lbo_a, 1024);
+            const uint64_t db = make_sw128_desc(sb + k * kstep_b, lbo_b, 1024);
+            umma_bf16_ss_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[stage]);
+          if (++stage == kPairStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit_pair(&tmem_full[as]);
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue (both CTAs) ----------------------
+    const int ew = warp - 4;
+    int as = 0;
+    uint32_t aphase = 0;
+    const uint32_t leader_empty0 = mapa_u32(smem_u32(&tmem_empty[0]), 0);
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      int tm, tn;
+      tile_coords(tile, tiles_m, tiles_n, tm, tn);
+      const int row = tm * 2 * kBM + static_cast<int>(rank) * kBM + ew * 32 + lane;
+      const int n0 = tn * kPairBN;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kPairBN;
+#pragma unroll 1
+      for (int c = 0; c < kPairBN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        store_acc_chunk(r, Cout, row, n0 + c * 32, M, N, ldc, out_mode);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(leader_empty0 + as * 8);
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<2 * kPairBN>(tmem_base);
   }
 }
 
@@ -301,9 +488,43 @@ int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, in
   return 0;
 }
 
+template <bool kAMN, bool kBMN>
+int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, int K,
+                     long long ldc, int out_mode, int max_ctas, cudaStream_t stream) {
+  auto kern = gemm_bf16_pair_kernel<kAMN, kBMN>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         PairSmem::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + kPairBN - 1) / kPairBN);
+  int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
+  if (max_ctas > 1 && pairs > max_ctas / 2) pairs = max_ctas / 2;
+  kern<<<2 * pairs, kGemmThreads, PairSmem::kTotal, stream>>>(ta, tb, C, M, N, K, ldc, out_mode);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
 }  // namespace b200
 
 using namespace b200;
+
+// variant: 0 = choose (CTA pairs when the problem has at least one 256 x 256 tile),
+// 1 = force the single-CTA kernel, 2 = force the CTA-pair kernel.
+static int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K,
+                         int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                         long long ldc, int out_mode, int max_ctas, int variant,
+                         cudaStream_t stream);
+
+B200_API int b200_gemm_bf16_variant(const void* A, const void* B, void* C, int M, int N, int K,
+                                    int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                                    long long ldc, int out_mode, int max_ctas, int variant,
+                                    cudaStream_t stream) {
+  return gemm_dispatch(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, out_mode, max_ctas,
+                       variant, stream);
+}
 
 // See the header comment for the operand conventions. lda/ldb/ldc are row strides in
 // elements of the STORED matrices. max_ctas > 0 caps the persistent grid (used to leave
@@ -311,13 +532,37 @@ using namespace b200;
 B200_API int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                             int a_mn_major, int b_mn_major, long long lda, long long ldb,
                             long long ldc, int out_mode, int max_ctas, cudaStream_t stream) {
+  return gemm_dispatch(A, B, C, M, N, K, a_mn_major, b_mn_major, lda, ldb, ldc, out_mode, max_ctas,
+                       0, stream);
+}
+
+static int gemm_dispatch(const void* A, const void* B, void* C, int M, int N, int K,
+                         int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                         long long ldc, int out_mode, int max_ctas, int variant,
+                         cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return B200_ERR_BAD_ARG;
   if ((lda % 8) || (ldb % 8) || out_mode < 0 || out_mode > 2) return B200_ERR_UNSUPPORTED;
   if ((reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15))
     return B200_ERR_UNSUPPORTED;
-  const int BN = N > 128 ? 256 : 128;
   CUtensorMap ta, tb;
   int rc;
+  const bool pair = variant == 2 || (variant == 0 && M >= 2 * kBM && N >= kPairBN && max_ctas != 1);
+  if (pair) {
+    if (!a_mn_major) rc = make_tmap_2d(&ta, A, M, K, lda, kBM);
+    else rc = make_tmap_2d(&ta, A, K, M, lda, kBK);
+    if (rc) return rc;
+    if (!b_mn_major) rc = make_tmap_2d(&tb, B, N, K, ldb, kPairHalfN);
+    else rc = make_tmap_2d(&tb, B, K, N, ldb, kBK);
+    if (rc) return rc;
+    if (!a_mn_major && !b_mn_major)
+      return launch_gemm_pair<false, false>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);
+    if (!a_mn_major && b_mn_major)
+      return launch_gemm_pair<false, true>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);
+    if (a_mn_major && !b_mn_major)
+      return launch_gemm_pair<true, false>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);
+    return launch_gemm_pair<true, true>(ta, tb, C, M, N, K, ldc, out_mode, max_ctas, stream);
+  }
+  const int BN = N > 128 ? 256 : 128;
   if (!a_mn_major) rc = make_tmap_2d(&ta, A, M, K, lda, kBM);
   else rc = make_tmap_2d(&ta, A, K, M, lda, kBK);
   if (rc) return rc;

@@ -449,9 +449,17 @@ def _own_gemm_ok(*ts):
         and _MODE != "off"
 
 
+def _use_own(M, N, K, force_own):
+    """`auto` takes the tcgen05 CTA-pair kernel for every GEMM with at least one full 256 x 256
+    tile; tiny problems stay on the library (launch-bound either way)."""
+    if force_own or _GEMM_MODE == "own":
+        return True
+    return _GEMM_MODE == "auto" and M >= 256 and N >= 256 and K >= 64
+
+
 def gemm_nt(x2d, w, force_own=False):
     """x2d [M,K] @ w[N,K]^T -> [M,N]."""
-    if (force_own or _GEMM_MODE == "own") and _own_gemm_ok(x2d, w):
+    if _use_own(x2d.shape[0], w.shape[0], x2d.shape[1], force_own) and _own_gemm_ok(x2d, w):
         M, K = x2d.shape
         N = w.shape[0]
         out = torch.empty(M, N, device=x2d.device, dtype=torch.bfloat16)
@@ -463,7 +471,7 @@ def gemm_nt(x2d, w, force_own=False):
 
 def gemm_nn(dy2d, w, force_own=False):
     """dy2d [M,N] @ w[N,K] -> [M,K] (dgrad)."""
-    if (force_own or _GEMM_MODE == "own") and _own_gemm_ok(dy2d, w):
+    if _use_own(dy2d.shape[0], w.shape[1], dy2d.shape[1], force_own) and _own_gemm_ok(dy2d, w):
         M, N = dy2d.shape
         K = w.shape[1]
         out = torch.empty(M, K, device=dy2d.device, dtype=torch.bfloat16)

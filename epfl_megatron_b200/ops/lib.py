@@ -44,6 +44,7 @@ _SIGNATURES = {
     "b200_sumsq": ([vp, i64, vp, vp, i32, vp], i32),
     "b200_scale": ([vp, i64, vp, f32, vp], i32),
     "b200_gemm_bf16": ([vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, i32, vp], i32),
+    "b200_gemm_bf16_variant": ([vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, i32, i32, vp], i32),
     "b200_attn_fwd": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                        i64, i64, f32, i32, vp], i32),
 }

@@ -323,17 +323,17 @@ def check_casts(n=1 << 20):
     return {}
 
 
-def gemm(a, b, M, N, K, a_mn, b_mn, out_mode, c=None, max_ctas=0):
-    """Thin wrapper used by checks and by ops.linear."""
+def gemm(a, b, M, N, K, a_mn, b_mn, out_mode, c=None, max_ctas=0, kernel=0):
+    """Thin wrapper used by checks and by ops.linear. kernel: 0 auto, 1 single CTA, 2 CTA pair."""
     if c is None:
         c = torch.empty(M, N, device=a.device,
                         dtype=torch.bfloat16 if out_mode == 0 else torch.float32)
-    L.call("b200_gemm_bf16", a.data_ptr(), b.data_ptr(), c.data_ptr(), M, N, K, a_mn, b_mn,
-           a.stride(0), b.stride(0), c.stride(0), out_mode, max_ctas, L.stream_ptr())
+    L.call("b200_gemm_bf16_variant", a.data_ptr(), b.data_ptr(), c.data_ptr(), M, N, K, a_mn, b_mn,
+           a.stride(0), b.stride(0), c.stride(0), out_mode, max_ctas, kernel, L.stream_ptr())
     return c
 
 
-def check_gemm(variant="nt", M=512, N=768, K=512, out_mode=0):
+def check_gemm(variant="nt", M=512, N=768, K=512, out_mode=0, kernel=0):
     """variant: nt (fwd), nn (dgrad: B MN-major), tn (wgrad: both MN-major), tt."""
     dev = _dev()
     torch.manual_seed(9)
@@ -347,9 +347,9 @@ def check_gemm(variant="nt", M=512, N=768, K=512, out_mode=0):
     if out_mode == 2:
         c = torch.randn(M, N, device=dev)
         ref = ref + c
-        out = gemm(a_st, b_st, M, N, K, int(a_mn), int(b_mn), 2, c=c)
+        out = gemm(a_st, b_st, M, N, K, int(a_mn), int(b_mn), 2, c=c, kernel=kernel)
     else:
-        out = gemm(a_st, b_st, M, N, K, int(a_mn), int(b_mn), out_mode)
+        out = gemm(a_st, b_st, M, N, K, int(a_mn), int(b_mn), out_mode, kernel=kernel)
     tol = 0.02 * math.sqrt(K) if out_mode == 0 else 1e-2 * math.sqrt(K) * 0.1
     return _close(out, ref, tol, 1e-2, f"gemm {variant} {M}x{N}x{K} mode{out_mode}")
 
@@ -413,6 +413,18 @@ CHECKS = {
     "adam": check_adam,
     "casts": check_casts,
     "gemm_nt": lambda: check_gemm("nt"),
+    "gemm_nt_1cta": lambda: check_gemm("nt", kernel=1),
+    "gemm_nt_1cta_big": lambda: check_gemm("nt", 2048, 2048, 1024, kernel=1),
+    "gemm_nn_1cta": lambda: check_gemm("nn", kernel=1),
+    "gemm_tn_1cta_acc": lambda: check_gemm("tn", 768, 1024, 2048, out_mode=2, kernel=1),
+    "gemm_nt_pair": lambda: check_gemm("nt", kernel=2),
+    "gemm_nt_pair_small": lambda: check_gemm("nt", 128, 128, 64, kernel=2),
+    "gemm_nt_pair_ragged": lambda: check_gemm("nt", 1000, 968, 520, kernel=2),
+    "gemm_nn_pair": lambda: check_gemm("nn", 1024, 1280, 768, kernel=2),
+    "gemm_tn_pair": lambda: check_gemm("tn", 1024, 1280, 768, kernel=2),
+    "gemm_tt_pair": lambda: check_gemm("tt", 512, 768, 512, kernel=2),
+    "gemm_tn_pair_acc": lambda: check_gemm("tn", 768, 1024, 2048, out_mode=2, kernel=2),
+    "gemm_nt_pair_f32": lambda: check_gemm("nt", 512, 512, 256, out_mode=1, kernel=2),
     "gemm_nt_big": lambda: check_gemm("nt", 4096, 4096, 4096),
     "gemm_nt_ragged": lambda: check_gemm("nt", 1000, 968, 520),
     "gemm_nn": lambda: check_gemm("nn"),

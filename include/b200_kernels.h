@@ -119,6 +119,13 @@ int b200_scale(float* x, long long n, const float* coef, float host_coef, cudaSt
 int b200_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn_major,
                    int b_mn_major, long long lda, long long ldb, long long ldc, int out_mode,
                    int max_ctas, cudaStream_t stream);
+/* Same GEMM with the kernel chosen by the caller: variant 0 = automatic (CTA pairs, i.e.
+ * tcgen05.mma.cta_group::2 over 256 x 256 tiles, whenever M >= 256 and N >= 256), 1 = single-CTA
+ * 128 x 256 tiles, 2 = CTA pairs. Same reference call sites as b200_gemm_bf16. */
+int b200_gemm_bf16_variant(const void* A, const void* B, void* C, int M, int N, int K,
+                           int a_mn_major, int b_mn_major, long long lda, long long ldb,
+                           long long ldc, int out_mode, int max_ctas, int variant,
+                           cudaStream_t stream);
 
 /* ---- tcgen05 attention (csrc/attn_fwd_tcgen05.cu) --------------------------------------- */
 /* Causal / full GQA attention forward reading q, k, v through arbitrary element strides

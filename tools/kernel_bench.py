@@ -68,10 +68,12 @@ def bench_gemm():
         B = torch.randn(N, K, device="cuda").bfloat16()
         C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
         fl = 2.0 * M * N * K
-        t_own = timeit(lambda: SC.gemm(A, B, M, N, K, 0, 0, 0, c=C))
+        t_own = timeit(lambda: SC.gemm(A, B, M, N, K, 0, 0, 0, c=C, kernel=2))
+        t_1cta = timeit(lambda: SC.gemm(A, B, M, N, K, 0, 0, 0, c=C, kernel=1))
         t_lib = timeit(lambda: torch.matmul(A, B.t(), out=C))
-        report(kernel="gemm_nt", shape=name, M=M, N=N, K=K, ms_own=t_own, ms_cublas=t_lib,
-               tflops_own=fl / t_own / 1e9, tflops_cublas=fl / t_lib / 1e9,
+        report(kernel="gemm_nt", shape=name, M=M, N=N, K=K, ms_own=t_own, ms_own_1cta=t_1cta,
+               ms_cublas=t_lib, tflops_own=fl / t_own / 1e9, tflops_own_1cta=fl / t_1cta / 1e9,
+               tflops_cublas=fl / t_lib / 1e9,
                frac_of_measured_peak=fl / t_own / 1e9 / PEAKS["bf16_tflops"])
     # dgrad / wgrad forms on the MLP shape
     M, N, K = 4096, 11008, 4096
@@ -85,11 +87,13 @@ def bench_gemm():
            tflops_own=2.0 * M * N * K / t_own / 1e9, tflops_cublas=2.0 * M * N * K / t_lib / 1e9)
     G = torch.zeros(N, K, device="cuda")
     t_own = timeit(lambda: SC.gemm(dY, X, N, K, M, 1, 1, 2, c=G))
+    t_1cta = timeit(lambda: SC.gemm(dY, X, N, K, M, 1, 1, 2, c=G, kernel=1))
 
     def lib_wgrad():
         G.add_(torch.matmul(dY.t(), X))
     t_lib = timeit(lib_wgrad)
-    report(kernel="gemm_wgrad_accum_fp32", M=N, N=K, K=M, ms_own=t_own, ms_cublas_plus_add=t_lib,
+    report(kernel="gemm_wgrad_accum_fp32", M=N, N=K, K=M, ms_own=t_own, ms_own_1cta=t_1cta,
+           ms_cublas_plus_add=t_lib,
            tflops_own=2.0 * M * N * K / t_own / 1e9, tflops_lib=2.0 * M * N * K / t_lib / 1e9)
 
 

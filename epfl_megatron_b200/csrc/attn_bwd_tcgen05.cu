@@ -1,0 +1,650 @@
+// Causal / full GQA-native attention backward on tcgen05 + TMEM (K12 of SURVEY.md
+// section 8). Replaces the FlashAttention-2 backward the reference reaches through
+// flash_attn_func at megatron/model/transformer.py:514-522 (and the K/V head expansion in
+// front of it, :448-455, whose backward is a reduction over the expanded heads).
+//
+// Two passes over the same 128 x 128 score tiles, each a CTA with one STATIONARY operand
+// pair kept in shared memory and one STREAMED pair in a 2-stage TMA ring:
+//
+//   pass KV (template kIsKV = true): stationary K_j, V_j; streams Q_i, dO_i of every query
+//     head of the KV group and every query block that sees block j.
+//       S^T  = K_j Q_i^T          tcgen05.mma  -> TMEM region A
+//       dP^T = V_j dO_i^T         tcgen05.mma  -> TMEM region B
+//       P^T  = exp2(S^T * scale*log2e - LSE)          (8 warps, one kv row per thread)
+//       dS^T = P^T o (dP^T - D)
+//       dV_j += P^T dO_i          A operand read from TMEM (bf16 P^T written over region A)
+//       dK_j += dS^T Q_i          A operand read from TMEM (bf16 dS^T written over region B)
+//     The GQA reduction of dK / dV over the query heads of a group happens in the TMEM
+//     accumulators, so K/V are never expanded and no atomics are needed.
+//   pass Q (kIsKV = false): stationary Q_i, dO_i; streams K_j, V_j.
+//       S = Q_i K_j^T (double-buffered in TMEM), dP = dO_i V_j^T, dS = P o (dP - D),
+//       dQ_i += dS K_j            A operand read from TMEM
+//     Recomputing S/dP costs two extra MMAs per tile but removes the fp32 dQ atomics and the
+//     conversion pass of the single-pass formulation.
+//
+// All operands come straight out of the fused projection output [s, b, g, q_per_g+2, hn]
+// (rank-5 / rank-4 TMA maps, any strides) and dQ/dK/dV are written straight into the
+// gradient of that tensor. A small pre-pass computes D = rowsum(dO o O) and LSE*log2e
+// into caller-provided scratch padded to a multiple of 128 rows.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kBwdT = 128;        // tile edge (query rows, kv rows, head dim)
+constexpr int kBwdThreads = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, warps 4-11 math
+constexpr int kTileBytes = kBwdT * kBwdT * 2;  // 32 KB: two [128 x 128 B] swizzled boxes
+constexpr int kBoxBytes = kBwdT * 128;         // 16 KB
+
+struct BwdSmem {
+  static constexpr int kXa = 0;
+  static constexpr int kXb = kXa + kTileBytes;
+  static constexpr int kY = kXb + kTileBytes;          // stage s: Ya at kY + s*64K, Yb + 32K
+  static constexpr int kVec = kY + 4 * kTileBytes;     // stage s: lse2[128], D[128] fp32
+  static constexpr int kBar = kVec + 2 * 1024;
+  static constexpr int kTotal = kBar + 256 + 1024;
+};
+
+__device__ __forceinline__ void tma_load_5d_b(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
+                                              int c0, int c1, int c2, int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0),
+      "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes,
+                                             uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes),
+      "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]),
+      "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]),
+      "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait_b() {
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]: the A operand (bf16 pairs, one row per TMEM lane) is read
+// from tensor memory.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
+                                             uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// ---------------------------------------------------------------------------------
+// pre-pass: D[b, head, s] = sum_d O * dO, LSE2 = LSE * log2(e); rows s >= sq get
+// D = 0, LSE2 = +inf (so P = 0 there). One warp per (b, head, s) row.
+// ---------------------------------------------------------------------------------
+__global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ o,
+                                     const __nv_bfloat16* __restrict__ dout,
+                                     const float* __restrict__ lse, float* __restrict__ lse2,
+                                     float* __restrict__ dvec, int sq, int s_pad, int B, int np) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  const int total = B * np * s_pad;
+  if (row >= total) return;
+  const int s = row % s_pad;
+  const int bh = row / s_pad;
+  const int head = bh % np, b = bh / np;
+  if (s >= sq) {
+    if (lane == 0) {
+      lse2[row] = INFINITY;
+      dvec[row] = 0.f;
+    }
+    return;
+  }
+  const size_t off = ((size_t)s * B + b) * ((size_t)np * kBwdT) + (size_t)head * kBwdT + lane * 4;
+  const uint2 ov = *reinterpret_cast<const uint2*>(o + off);
+  const uint2 dv = *reinterpret_cast<const uint2*>(dout + off);
+  const float2 o0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ov.x));
+  const float2 o1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&ov.y));
+  const float2 d0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&dv.x));
+  const float2 d1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&dv.y));
+  float acc = o0.x * d0.x + o0.y * d0.y + o1.x * d1.x + o1.y * d1.y;
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    dvec[row] = acc;
+    lse2[row] = lse[((size_t)b * np + head) * sq + s] * 1.4426950408889634f;
+  }
+}
+
+// fp32 partial dK / dV sums [2][sk][B][G][128] -> bf16 at their strided destinations.
+__global__ void attn_bwd_kv_convert_kernel(const float* __restrict__ kv_acc,
+                                           __nv_bfloat16* __restrict__ dk,
+                                           __nv_bfloat16* __restrict__ dv, long long o_ss,
+                                           long long o_sb, long long o_sg, int sk, int B, int G) {
+  const long long rows = (long long)sk * B * G;
+  const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one per 8 elements
+  if (idx >= 2 * rows * (kBwdT / 8)) return;
+  const int c8 = idx % (kBwdT / 8);
+  long long row = idx / (kBwdT / 8);
+  const int which = row >= rows;
+  row -= which * rows;
+  const int g = row % G;
+  const int b = (row / G) % B;
+  const long long s = row / ((long long)G * B);
+  const float4* src = reinterpret_cast<const float4*>(kv_acc + (which * rows + row) * kBwdT + c8 * 8);
+  const float4 x = src[0], y = src[1];
+  uint4 w;
+  w.x = pack_bf16x2(x.x, x.y);
+  w.y = pack_bf16x2(x.z, x.w);
+  w.z = pack_bf16x2(y.x, y.y);
+  w.w = pack_bf16x2(y.z, y.w);
+  __nv_bfloat16* dst = (which ? dv : dk) + s * o_ss + b * o_sb + g * o_sg + c8 * 8;
+  *reinterpret_cast<uint4*>(dst) = w;
+}
+
+// ---------------------------------------------------------------------------------
+// main kernel, both passes
+// ---------------------------------------------------------------------------------
+// maps: tmQ rank 5 {hn, s, j, g, b}; tmK / tmV rank 4 {hn, s, g, b}; tmdO rank 4 {hn, s, head, b}
+template <bool kIsKV>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                const float* __restrict__ lse2, const float* __restrict__ dvec,
+                __nv_bfloat16* __restrict__ g0, __nv_bfloat16* __restrict__ g1, long long o_ss,
+                long long o_sb, long long o_sg, long long o_sj, int sq, int sk, int s_pad, int B,
+                int G, int qpg, float scale, int causal, int nsplit, float* __restrict__ kv_acc) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::kBar);
+  uint64_t* x_full = bars + 0;
+  uint64_t* y_full = bars + 1;    // [2]
+  uint64_t* y_empty = bars + 3;   // [2]
+  uint64_t* s_full = bars + 5;    // [2]
+  uint64_t* dp_full = bars + 7;
+  uint64_t* p_ready = bars + 8;
+  uint64_t* ds_ready = bars + 9;
+  uint64_t* acc_done = bars + 10;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int np = G * qpg;
+  const int nq = (sq + kBwdT - 1) / kBwdT, nkv = (sk + kBwdT - 1) / kBwdT;
+  const int shift = sk - sq;  // query i sees keys <= i + shift when causal
+  const int b = blockIdx.z;
+  // KV pass with nsplit > 1: CTA `split` of a (kv block, group) owns query heads
+  // [split * qpg/nsplit, (split+1) * qpg/nsplit) and adds its partial dK/dV into kv_acc.
+  const int jj0 = kIsKV ? (blockIdx.y % nsplit) * (qpg / nsplit) : 0;
+  const float scale_log2 = scale * 1.4426950408889634f;
+
+  // iteration space of this CTA
+  int g, head = 0, xblk, y_first, y_count, n_iter;
+  if (kIsKV) {
+    xblk = blockIdx.x;  // kv block; low blocks see the most queries, so they go first
+    g = blockIdx.y / nsplit;
+    // first query block with any visible pair: q + shift >= xblk*128
+    y_first = causal ? max(0, (xblk * kBwdT - shift) / kBwdT) : 0;
+    y_count = max(0, nq - y_first);
+    n_iter = y_count * (qpg / nsplit);  // this CTA's share of the group's query heads
+  } else {
+    xblk = nq - 1 - blockIdx.x;  // query block; late blocks see the most keys
+    head = blockIdx.y;
+    g = head / qpg;
+    y_first = 0;
+    y_count = causal ? min(nkv, (xblk * kBwdT + kBwdT - 1 + shift) / kBwdT + 1) : nkv;
+    n_iter = y_count;
+  }
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmdO);
+    mbar_init(x_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&y_full[i], 1);
+      mbar_init(&y_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+    }
+    mbar_init(dp_full, 1);
+    mbar_init(p_ready, 256);
+    mbar_init(ds_ready, 256);
+    mbar_init(acc_done, 1);
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  // TMEM columns. KV pass: A = S^T/P^T, B = dP^T/dS^T, ACC1 = dV, ACC2 = dK.
+  // Q pass: S double-buffered at 0 / 128, B = dP/dS at 256, ACC = dQ at 384.
+  const uint32_t tm_A = tmem_base;
+  const uint32_t tm_B = tmem_base + (kIsKV ? 128 : 256);
+  const uint32_t tm_acc1 = tmem_base + 256;  // KV pass only
+  const uint32_t tm_acc2 = tmem_base + 384;
+
+  uint8_t* sXa = smem + BwdSmem::kXa;
+  uint8_t* sXb = smem + BwdSmem::kXb;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer ------------------------------
+    if (lane == 0 && n_iter > 0) {
+      mbar_expect_tx(x_full, 2 * kTileBytes);
+      if (kIsKV) {
+        tma_load_4d(sXa, &tmK, x_full, 0, xblk * kBwdT, g, b);
+        tma_load_4d(sXa + kBoxBytes, &tmK, x_full, 64, xblk * kBwdT, g, b);
+        tma_load_4d(sXb, &tmV, x_full, 0, xblk * kBwdT, g, b);
+        tma_load_4d(sXb + kBoxBytes, &tmV, x_full, 64, xblk * kBwdT, g, b);
+      } else {
+        const int j = head - g * qpg;
+        tma_load_5d_b(sXa, &tmQ, x_full, 0, xblk * kBwdT, j, g, b);
+        tma_load_5d_b(sXa + kBoxBytes, &tmQ, x_full, 64, xblk * kBwdT, j, g, b);
+        tma_load_4d(sXb, &tmdO, x_full, 0, xblk * kBwdT, head, b);
+        tma_load_4d(sXb + kBoxBytes, &tmdO, x_full, 64, xblk * kBwdT, head, b);
+      }
+      for (int it = 0; it < n_iter; ++it) {
+        const int st = it & 1;
+        mbar_wait(&y_empty[st], ((it >> 1) & 1) ^ 1);
+        uint8_t* sYa = smem + BwdSmem::kY + st * 2 * kTileBytes;
+        uint8_t* sYb = sYa + kTileBytes;
+        if (kIsKV) {
+          const int jl = it / y_count, yb = y_first + it - jl * y_count;
+          const int jj = jj0 + jl;
+          const int hd = g * qpg + jj;
+          float* vec = reinterpret_cast<float*>(smem + BwdSmem::kVec + st * 1024);
+          const size_t voff = ((size_t)b * np + hd) * s_pad + (size_t)yb * kBwdT;
+          mbar_expect_tx(&y_full[st], 2 * kTileBytes + 1024);
+          tma_load_5d_b(sYa, &tmQ, &y_full[st], 0, yb * kBwdT, jj, g, b);
+          tma_load_5d_b(sYa + kBoxBytes, &tmQ, &y_full[st], 64, yb * kBwdT, jj, g, b);
+          tma_load_4d(sYb, &tmdO, &y_full[st], 0, yb * kBwdT, hd, b);
+          tma_load_4d(sYb + kBoxBytes, &tmdO, &y_full[st], 64, yb * kBwdT, hd, b);
+          bulk_load_1d(vec, lse2 + voff, 512, &y_full[st]);
+          bulk_load_1d(vec + 128, dvec + voff, 512, &y_full[st]);
+        } else {
+          const int yb = y_first + it;
+          mbar_expect_tx(&y_full[st], 2 * kTileBytes);
+          tma_load_4d(sYa, &tmK, &y_full[st], 0, yb * kBwdT, g, b);
+          tma_load_4d(sYa + kBoxBytes, &tmK, &y_full[st], 64, yb * kBwdT, g, b);
+          tma_load_4d(sYb, &tmV, &y_full[st], 0, yb * kBwdT, g, b);
+          tma_load_4d(sYb + kBoxBytes, &tmV, &y_full[st], 64, yb * kBwdT, g, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer --------------------------------
+    if (lane == 0 && n_iter > 0) {
+      constexpr uint32_t idesc_ss = make_idesc_bf16(kBwdT, kBwdT, 0, 0);
+      constexpr uint32_t idesc_ts = make_idesc_bf16(kBwdT, kBwdT, 0, 1);
+      const uint32_t aXa = smem_u32(sXa), aXb = smem_u32(sXb);
+      const uint32_t aY = smem_u32(smem + BwdSmem::kY);
+      // D = X * Y^T, both K-major with the head dim split into two 64-wide boxes
+      auto mma_xyT = [&](uint32_t d, uint32_t x, uint32_t y) {
+#pragma unroll
+        for (int k = 0; k < kBwdT / 16; ++k) {
+          const uint32_t off = (k >> 2) * kBoxBytes + (k & 3) * 32;
+          umma_bf16_ss(d, make_sw128_desc(x + off, 16, 1024), make_sw128_desc(y + off, 16, 1024),
+                       idesc_ss, k != 0);
+        }
+      };
+      // D += A(tmem, bf16 pairs) * Y with Y [128 rows (K) x 128 (N)] as stored: MN-major B,
+      // 16 rows per MMA = 2 KB, the two 64-wide N chunks one box apart.
+      auto mma_tmem_y = [&](uint32_t d, uint32_t a, uint32_t y, bool first) {
+#pragma unroll
+        for (int k = 0; k < kBwdT / 16; ++k) {
+          const uint32_t acol = k < 4 ? k * 8 : 64 + (k - 4) * 8;
+          umma_bf16_ts(d, a + acol, make_sw128_desc(y + k * 2048, kBoxBytes, 1024), idesc_ts,
+                       (first && k == 0) ? 0u : 1u);
+        }
+      };
+      mbar_wait(x_full, 0);
+      mbar_wait(&y_full[0], 0);
+      tc_fence_after();
+      if (kIsKV) {
+        mma_xyT(tm_A, aXa, aY);
+        umma_commit(&s_full[0]);
+        mma_xyT(tm_B, aXb, aY + kTileBytes);
+        umma_commit(dp_full);
+        for (int it = 0; it < n_iter; ++it) {
+          const int st = it & 1;
+          const uint32_t ya = aY + st * 2 * kTileBytes, yb = ya + kTileBytes;
+          mbar_wait(p_ready, it & 1);
+          tc_fence_after();
+          mma_tmem_y(tm_acc1, tm_A, yb, it == 0);            // dV += P^T dO
+          if (it + 1 < n_iter) {
+            mbar_wait(&y_full[st ^ 1], ((it + 1) >> 1) & 1);
+            tc_fence_after();
+            mma_xyT(tm_A, aXa, aY + (st ^ 1) * 2 * kTileBytes);
+            umma_commit(&s_full[0]);
+          }
+          mbar_wait(ds_ready, it & 1);
+          tc_fence_after();
+          mma_tmem_y(tm_acc2, tm_B, ya, it == 0);            // dK += dS^T Q
+          umma_commit(&y_empty[st]);
+          if (it + 1 < n_iter) {
+            mma_xyT(tm_B, aXb, aY + (st ^ 1) * 2 * kTileBytes + kTileBytes);
+            umma_commit(dp_full);
+          }
+        }
+      } else {
+        mma_xyT(tm_A, aXa, aY);
+        umma_commit(&s_full[0]);
+        mma_xyT(tm_B, aXb, aY + kTileBytes);
+        umma_commit(dp_full);
+        if (n_iter > 1) {
+          mbar_wait(&y_full[1], 0);
+          tc_fence_after();
+          mma_xyT(tm_A + 128, aXa, aY + 2 * kTileBytes);
+          umma_commit(&s_full[1]);
+        }
+        for (int it = 0; it < n_iter; ++it) {
+          const int st = it & 1;
+          const uint32_t ya = aY + st * 2 * kTileBytes;
+          mbar_wait(ds_ready, it & 1);
+          tc_fence_after();
+          mma_tmem_y(tm_acc2, tm_B, ya, it == 0);            // dQ += dS K
+          umma_commit(&y_empty[st]);
+          if (it + 1 < n_iter) {
+            mma_xyT(tm_B, aXb, aY + (st ^ 1) * 2 * kTileBytes + kTileBytes);
+            umma_commit(dp_full);
+          }
+          if (it + 2 < n_iter) {
+            mbar_wait(&y_full[st], ((it + 2) >> 1) & 1);
+            tc_fence_after();
+            mma_xyT(tm_A + st * 128, aXa, ya);
+            umma_commit(&s_full[st]);
+          }
+        }
+      }
+      umma_commit(acc_done);
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ math warps --------------------------------
+    const int quarter = warp & 3;         // TMEM lane quarter this warp may touch
+    const int half = (warp - 4) >> 2;     // which 64 of the 128 columns
+    const int r = quarter * 32 + lane;    // row inside the tile == TMEM lane
+    const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
+    const int xrow = xblk * kBwdT + r;    // kv index (KV pass) or query index (Q pass)
+    float my_lse2 = 0.f, my_d = 0.f;
+    if (!kIsKV) {
+      const size_t voff = ((size_t)b * np + head) * s_pad + xrow;
+      my_lse2 = lse2[voff];
+      my_d = dvec[voff];
+    }
+    for (int it = 0; it < n_iter; ++it) {
+      const int st = it & 1;
+      int yb;
+      if (kIsKV) {
+        const int jj = it / y_count;
+        yb = y_first + it - jj * y_count;
+        mbar_wait(&y_full[st], (it >> 1) & 1);  // LSE / D vectors of this stage
+      } else {
+        yb = y_first + it;
+      }
+      const float* vec = reinterpret_cast<const float*>(smem + BwdSmem::kVec + st * 1024);
+      const int ycol0 = yb * kBwdT + half * 64;
+      // does this tile need the causal test at all?
+      bool need_mask;
+      if (kIsKV) need_mask = causal && (xblk * kBwdT + kBwdT - 1 > yb * kBwdT + shift);
+      else need_mask = (causal && (yb * kBwdT + kBwdT - 1 > xblk * kBwdT + shift)) ||
+                       (yb * kBwdT + kBwdT > sk);
+      const uint32_t tS = kIsKV ? tm_A : tm_A + st * 128;
+      mbar_wait(&s_full[kIsKV ? 0 : st], kIsKV ? (it & 1) : ((it >> 1) & 1));
+      tc_fence_after();
+      float P[64];
+#pragma unroll
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t sr[32];
+        tmem_ld_32x32(tS + lane_off + half * 64 + ch * 32, sr);
+        tmem_ld_wait();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+          const int c = half * 64 + ch * 32 + t;
+          const float l2 = kIsKV ? vec[c] : my_lse2;
+          float p = exp2f(__uint_as_float(sr[t]) * scale_log2 - l2);
+          if (need_mask) {
+            const int ycol = ycol0 + ch * 32 + t;
+            bool vis;
+            if (kIsKV) vis = xrow <= ycol + shift;                 // kv <= q + shift
+            else vis = (!causal || ycol <= xrow + shift) && ycol < sk;
+            p = vis ? p : 0.f;
+          }
+          P[ch * 32 + t] = p;
+        }
+        if (kIsKV) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int t = 0; t < 16; ++t) pk[t] = pack_bf16x2(P[ch * 32 + 2 * t], P[ch * 32 + 2 * t + 1]);
+          tmem_st_32x16(tm_A + lane_off + half * 64 + ch * 16, pk);
+        }
+      }
+      if (kIsKV) {
+        tmem_st_wait_b();
+        tc_fence_before();
+        mbar_arrive(p_ready);
+      }
+      mbar_wait(dp_full, it & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t dr[32];
+        tmem_ld_32x32(tm_B + lane_off + half * 64 + ch * 32, dr);
+        tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+          const int c = half * 64 + ch * 32 + 2 * t;
+          const float d0 = kIsKV ? vec[128 + c] : my_d;
+          const float d1 = kIsKV ? vec[128 + c + 1] : my_d;
+          const float a = P[ch * 32 + 2 * t] * (__uint_as_float(dr[2 * t]) - d0);
+          const float bb = P[ch * 32 + 2 * t + 1] * (__uint_as_float(dr[2 * t + 1]) - d1);
+          pk[t] = pack_bf16x2(a, bb);
+        }
+        tmem_st_32x16(tm_B + lane_off + half * 64 + ch * 16, pk);
+      }
+      tmem_st_wait_b();
+      tc_fence_before();
+      mbar_arrive(ds_ready);
+    }
+    // ------------------------------ epilogue ----------------------------------
+    if (n_iter > 0) {
+      mbar_wait(acc_done, 0);
+      tc_fence_after();
+    }
+    const bool row_ok = xrow < (kIsKV ? sk : sq);
+    const int jq = head - g * qpg;
+    // KV pass: g0 = dK (scaled), g1 = dV; Q pass: g0 = dQ (scaled)
+    const size_t rowoff = (size_t)xrow * o_ss + (size_t)b * o_sb + (size_t)g * o_sg +
+                          (kIsKV ? 0 : (size_t)jq * o_sj) + half * 64;
+    const bool split = kIsKV && nsplit > 1;
+    // fp32 partial sums: kv_acc[which][sk][B][G][128]
+    const size_t accoff = (((size_t)xrow * B + b) * G + g) * kBwdT + half * 64;
+    const size_t acc_plane = (size_t)sk * B * G * kBwdT;
+#pragma unroll 1
+    for (int which = 0; which < (kIsKV ? 2 : 1); ++which) {
+      const uint32_t acc = which == 0 ? tm_acc2 : tm_acc1;
+      __nv_bfloat16* dst = (which == 0 ? g0 : g1) + rowoff;
+      const float mul = which == 0 ? scale : 1.f;
+#pragma unroll 1
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t a[32];
+        if (n_iter > 0) {
+          tmem_ld_32x32(acc + lane_off + half * 64 + ch * 32, a);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int t = 0; t < 32; ++t) a[t] = 0u;
+        }
+        if (!row_ok) continue;
+        if (split) {
+          if (n_iter > 0) {
+            float* ap = kv_acc + which * acc_plane + accoff + ch * 32;
+#pragma unroll
+            for (int t = 0; t < 32; t += 4)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(ap + t),
+                           "f"(__uint_as_float(a[t]) * mul), "f"(__uint_as_float(a[t + 1]) * mul),
+                           "f"(__uint_as_float(a[t + 2]) * mul), "f"(__uint_as_float(a[t + 3]) * mul)
+                           : "memory");
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 w;
+            w.x = pack_bf16x2(__uint_as_float(a[8 * q + 0]) * mul, __uint_as_float(a[8 * q + 1]) * mul);
+            w.y = pack_bf16x2(__uint_as_float(a[8 * q + 2]) * mul, __uint_as_float(a[8 * q + 3]) * mul);
+            w.z = pack_bf16x2(__uint_as_float(a[8 * q + 4]) * mul, __uint_as_float(a[8 * q + 5]) * mul);
+            w.w = pack_bf16x2(__uint_as_float(a[8 * q + 6]) * mul, __uint_as_float(a[8 * q + 7]) * mul);
+            reinterpret_cast<uint4*>(dst + ch * 32)[q] = w;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+}  // namespace b200
+
+// ------------------------------- host side -----------------------------------
+namespace b200 {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode_fn();
+
+static int make_tmap_bwd(CUtensorMap* map, const void* base, int rank, const long long* dims,
+                         const long long* strides) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return B200_ERR_UNSUPPORTED;
+  cuuint64_t d[5];
+  cuuint64_t s[4];
+  cuuint32_t box[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    d[i] = (cuuint64_t)dims[i];
+    box[i] = 1;
+    es[i] = 1;
+    if (i > 0) {
+      if (strides[i - 1] % 8) return B200_ERR_UNSUPPORTED;
+      s[i - 1] = (cuuint64_t)strides[i - 1] * 2;
+    }
+  }
+  box[0] = 64;
+  box[1] = kBwdT;
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
+                  d, s, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : B200_ERR_BAD_ARG;
+}
+}  // namespace b200
+
+using namespace b200;
+
+// How many CTAs share the query heads of one (kv block, kv group) in the KV pass: enough to
+// fill the machine about twice when there are few KV heads (MQA / GQA under tensor parallelism).
+static int kv_pass_split(int sk, int B, int G, int qpg) {
+  const int nkv = (sk + kBwdT - 1) / kBwdT;
+  const long long ctas = (long long)nkv * G * B;
+  int want = (int)((2 * kNumSMs + ctas - 1) / ctas);
+  if (want <= 1) return 1;
+  int best = 1;
+  for (int d = 1; d <= qpg; ++d)
+    if (qpg % d == 0 && d <= want) best = d;
+  if (best < want)  // next divisor above `want`, if any
+    for (int d = best + 1; d <= qpg; ++d)
+      if (qpg % d == 0) { best = d; break; }
+  return best;
+}
+
+// fp32 elements of scratch b200_attn_bwd needs: LSE*log2e and D, each [B, np, ceil128(sq)],
+// plus the partial dK / dV sums [2, sk, B, G, 128] when the KV pass is split over query heads.
+B200_API long long b200_attn_bwd_scratch_elems(int sq, int sk, int B, int G, int qpg) {
+  const long long s_pad = (sq + kBwdT - 1) / kBwdT * kBwdT;
+  long long n = 2 * s_pad * B * G * qpg;
+  if (kv_pass_split(sk, B, G, qpg) > 1) n += 2LL * sk * B * G * kBwdT;
+  return n;
+}
+
+// q/k/v as in b200_attn_fwd. out, dout: [sq, B, G*qpg*128] bf16 contiguous; lse: [B, np, sq].
+// dq: element (s,b,g,j,d) at dq + s*dq_ss + b*dq_sb + g*dq_sg + j*dq_sj + d;
+// dk/dv: element (s,b,g,d) at dk + s*dk_ss + b*dk_sb + g*dk_sg + d.
+B200_API int b200_attn_bwd(const void* q, const void* k, const void* v, const void* out,
+                           const void* dout, const float* lse, void* dq, void* dk, void* dv,
+                           float* scratch, int sq, int sk, int B, int G, int qpg, int hn,
+                           long long q_ss, long long q_sb, long long q_sg, long long q_sj,
+                           long long k_ss, long long k_sb, long long k_sg, long long dq_ss,
+                           long long dq_sb, long long dq_sg, long long dq_sj, long long dk_ss,
+                           long long dk_sb, long long dk_sg, float softmax_scale, int causal,
+                           cudaStream_t stream) {
+  if (hn != kBwdT) return B200_ERR_UNSUPPORTED;
+  if (sq <= 0 || sk <= 0 || B <= 0 || G <= 0 || qpg <= 0 || !scratch) return B200_ERR_BAD_ARG;
+  if (causal && sk < sq) return B200_ERR_UNSUPPORTED;
+  if ((dq_ss | dq_sb | dq_sg | dq_sj | dk_ss | dk_sb | dk_sg) % 8) return B200_ERR_UNSUPPORTED;
+  const int np = G * qpg;
+  const int s_pad = (sq + kBwdT - 1) / kBwdT * kBwdT;
+  float* lse2 = scratch;
+  float* dvec = scratch + (size_t)s_pad * B * np;
+  float* kv_acc = scratch + 2 * (size_t)s_pad * B * np;
+  const int nsplit = kv_pass_split(sk, B, G, qpg);
+  CUtensorMap tq, tk, tv, tdo;
+  long long qd[5] = {hn, sq, qpg, G, B}, qs[4] = {q_ss, q_sj, q_sg, q_sb};
+  long long kd[4] = {hn, sk, G, B}, ks[3] = {k_ss, k_sg, k_sb};
+  long long od[4] = {hn, sq, np, B}, os[3] = {(long long)B * np * hn, hn, (long long)np * hn};
+  int rc = make_tmap_bwd(&tq, q, 5, qd, qs);
+  if (rc) return rc;
+  rc = make_tmap_bwd(&tk, k, 4, kd, ks);
+  if (rc) return rc;
+  rc = make_tmap_bwd(&tv, v, 4, kd, ks);
+  if (rc) return rc;
+  rc = make_tmap_bwd(&tdo, dout, 4, od, os);
+  if (rc) return rc;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel<true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(attn_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             BwdSmem::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  {
+    const int rows = B * np * s_pad;
+    attn_bwd_prep_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(
+        (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, lse, lse2, dvec, sq, s_pad, B, np);
+    B200_CHECK_LAUNCH();
+  }
+  const int nq = (sq + kBwdT - 1) / kBwdT, nkv = (sk + kBwdT - 1) / kBwdT;
+  if (nsplit > 1) {
+    cudaError_t e = cudaMemsetAsync(kv_acc, 0, 2 * (size_t)sk * B * G * kBwdT * sizeof(float), stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  attn_bwd_kernel<true><<<dim3(nkv, G * nsplit, B), kBwdThreads, BwdSmem::kTotal, stream>>>(
+      tq, tk, tv, tdo, lse2, dvec, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dk_ss, dk_sb, dk_sg, 0,
+      sq, sk, s_pad, B, G, qpg, softmax_scale, causal, nsplit, kv_acc);
+  B200_CHECK_LAUNCH();
+  if (nsplit > 1) {
+    const long long n8 = 2LL * sk * B * G * (kBwdT / 8);
+    attn_bwd_kv_convert_kernel<<<(unsigned)((n8 + 255) / 256), 256, 0, stream>>>(
+        kv_acc, (__nv_bfloat16*)dk, (__nv_bfloat16*)dv, dk_ss, dk_sb, dk_sg, sk, B, G);
+    B200_CHECK_LAUNCH();
+  }
+  attn_bwd_kernel<false><<<dim3(nq, np, B), kBwdThreads, BwdSmem::kTotal, stream>>>(
+      tq, tk, tv, tdo, lse2, dvec, (__nv_bfloat16*)dq, nullptr, dq_ss, dq_sb, dq_sg, dq_sj, sq, sk,
+      s_pad, B, G, qpg, softmax_scale, causal, 1, nullptr);
+  B200_CHECK_LAUNCH();
+  return 0;
+}

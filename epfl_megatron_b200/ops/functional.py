@@ -405,7 +405,13 @@ class _AttnFusedQKVFn(torch.autograd.Function):
         qpg = nslot - 2
         np_ = g * qpg
         dqkv = torch.empty_like(qkv)
-        # [b, s, heads, hn] strided views for the library backward (no copies when qpg == 1)
+        if not dout.is_contiguous():
+            dout = dout.contiguous()
+        if _ATTN_BWD == "own":
+            attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal)
+            return dqkv, None, None
+        # library backward (FlashAttention-2), kept for A/B runs: --b200_attn_bwd fa2
+        # [b, s, heads, hn] strided views (no copies when qpg == 1)
         k = qkv[:, :, :, qpg].permute(1, 0, 2, 3)
         v = qkv[:, :, :, qpg + 1].permute(1, 0, 2, 3)
         dk = dqkv[:, :, :, qpg].permute(1, 0, 2, 3)
@@ -422,6 +428,32 @@ class _AttnFusedQKVFn(torch.autograd.Function):
             _fa2_backward(do4, q, k, v, o4, lse, dq, dk, dv, scale, causal)
             dqkv[:, :, :, :qpg].copy_(dq.permute(1, 0, 2, 3).reshape(s, b, g, qpg, hn))
         return dqkv, None, None
+
+
+_ATTN_BWD = "own"   # own | fa2
+
+
+def set_attn_bwd_mode(mode: str):
+    global _ATTN_BWD
+    assert mode in ("own", "fa2")
+    _ATTN_BWD = mode
+
+
+def attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal=True):
+    """dqkv (same layout as qkv: [s, b, g, q_per_g+2, hn]) <- attention backward, own tcgen05
+    kernels (csrc/attn_bwd_tcgen05.cu). out/dout: [s, b, np*hn] contiguous, lse [b, np, s]."""
+    s, b, g, nslot, hn = qkv.shape
+    qpg = nslot - 2
+    n = L.lib().b200_attn_bwd_scratch_elems(s, s, b, g, qpg)
+    scratch = torch.empty(n, device=qkv.device, dtype=torch.float32)
+    ss, sb, sg, sj = qkv.stride(0), qkv.stride(1), qkv.stride(2), qkv.stride(3)
+    ds, db, dg, dj = dqkv.stride(0), dqkv.stride(1), dqkv.stride(2), dqkv.stride(3)
+    base, dbase = qkv.data_ptr(), dqkv.data_ptr()
+    L.call("b200_attn_bwd", base, base + qpg * sj * 2, base + (qpg + 1) * sj * 2, out.data_ptr(),
+           dout.data_ptr(), lse.data_ptr(), dbase, dbase + qpg * dj * 2, dbase + (qpg + 1) * dj * 2,
+           scratch.data_ptr(), s, s, b, g, qpg, hn, ss, sb, sg, sj, ss, sb, sg, ds, db, dg, dj,
+           ds, db, dg, float(scale), int(causal), L.stream_ptr(), launches=3)
+    return dqkv
 
 
 def attention_fused_qkv(qkv, scale=None, causal=True, dropout_p=0.0, attn_mask=None):

@@ -47,6 +47,10 @@ _SIGNATURES = {
     "b200_gemm_bf16_variant": ([vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, i32, i32, vp], i32),
     "b200_attn_fwd": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                        i64, i64, f32, i32, vp], i32),
+    "b200_attn_bwd_scratch_elems": ([i32, i32, i32, i32, i32], i64),
+    "b200_attn_bwd": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
+                       i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64,
+                       f32, i32, vp], i32),
 }
 
 _OPTIONAL = set()
@@ -133,7 +137,8 @@ def call(name: str, *args, launches: int = 1):
         if rc > 0:
             raise KernelError(f"{name}: CUDA error {rc}")
         raise KernelError(f"{name}: argument error {rc} "
-                          "(-1 bad argument, -2 unsupported shape/alignment, -3 too large)")
+                          "(-1 bad argument, -2 unsupported shape/alignment, -3 too large); "
+                          f"args={args!r}")
     _launches += launches
     return rc
 

@@ -401,6 +401,27 @@ def check_attn_fwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True):
     return st
 
 
+def check_attn_bwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True):
+    """Own backward vs autograd through the fp32 restatement of the same attention."""
+    from . import functional as Fn
+    dev = _dev()
+    torch.manual_seed(11)
+    qkv = torch.randn(S, B, G, QPG + 2, HN, device=dev).bfloat16()
+    dout = (torch.randn(S, B, G * QPG * HN, device=dev) * 0.5).bfloat16()
+    scale = 1.0 / math.sqrt(HN)
+    out, lse = attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, causal)
+    dqkv = torch.full_like(qkv, float("nan"))
+    Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal)
+    ref_in = qkv.float().requires_grad_()
+    q = ref_in[:, :, :, :QPG].reshape(S, B, G * QPG, HN)
+    ro, _ = attn_ref(q, ref_in[:, :, :, QPG], ref_in[:, :, :, QPG + 1], scale, causal)
+    ro.backward(dout.float().view(S, B, G * QPG, HN))
+    rg = ref_in.grad
+    return {"dq": _close(dqkv[:, :, :, :QPG], rg[:, :, :, :QPG], 3e-2, 3e-2, "attn dq"),
+            "dk": _close(dqkv[:, :, :, QPG], rg[:, :, :, QPG], 3e-2 * QPG ** 0.5, 3e-2, "attn dk"),
+            "dv": _close(dqkv[:, :, :, QPG + 1], rg[:, :, :, QPG + 1], 3e-2 * QPG ** 0.5, 3e-2, "attn dv")}
+
+
 CHECKS = {
     "rmsnorm": check_rmsnorm,
     "layernorm": check_layernorm,
@@ -435,6 +456,12 @@ CHECKS = {
     "attn_fwd": check_attn_fwd,
     "attn_fwd_mqa_long": lambda: check_attn_fwd(1024, 1, 1, 8, 128, True),
     "attn_fwd_full": lambda: check_attn_fwd(384, 1, 2, 2, 128, False),
+    "attn_bwd_small": lambda: check_attn_bwd(128, 1, 1, 1, 128, True),
+    "attn_bwd_mha": lambda: check_attn_bwd(512, 2, 4, 1, 128, True),
+    "attn_bwd_gqa": check_attn_bwd,
+    "attn_bwd_mqa_long": lambda: check_attn_bwd(1024, 1, 1, 8, 128, True),
+    "attn_bwd_full": lambda: check_attn_bwd(384, 1, 2, 2, 128, False),
+    "attn_bwd_ragged": lambda: check_attn_bwd(328, 1, 1, 2, 128, True),
 }
 
 

@@ -138,6 +138,20 @@ int b200_attn_fwd(const void* q, const void* k, const void* v, void* out, float*
                   long long q_sj, long long k_ss, long long k_sb, long long k_sg,
                   float softmax_scale, int causal, cudaStream_t stream);
 
+/* Attention backward (csrc/attn_bwd_tcgen05.cu): dq/dk/dv written with their own element strides,
+ * e.g. straight into the gradient of the fused QKV tensor; the GQA reduction of dk/dv over the
+ * query heads of a group happens in TMEM (plus fp32 partial sums in scratch when few KV heads would
+ * leave SMs idle). scratch: fp32 [b200_attn_bwd_scratch_elems(sq, sk, B, G, qpg)].
+ * out, dout: [sq, B, G*qpg*hn] bf16 contiguous; lse from b200_attn_fwd. hn must be 128.
+ * Reference: the FlashAttention-2 backward behind flash_attn_func, megatron/model/transformer.py:514-522. */
+long long b200_attn_bwd_scratch_elems(int sq, int sk, int B, int G, int qpg);
+int b200_attn_bwd(const void* q, const void* k, const void* v, const void* out, const void* dout,
+                  const float* lse, void* dq, void* dk, void* dv, float* scratch, int sq, int sk,
+                  int B, int G, int qpg, int hn, long long q_ss, long long q_sb, long long q_sg,
+                  long long q_sj, long long k_ss, long long k_sb, long long k_sg, long long dq_ss,
+                  long long dq_sb, long long dq_sg, long long dq_sj, long long dk_ss, long long dk_sb,
+                  long long dk_sg, float softmax_scale, int causal, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -129,6 +129,36 @@ def bench_attn():
         report(**rec)
 
 
+def bench_attn_bwd():
+    from epfl_megatron_b200.ops import functional as Fn
+    for name, S, B, G, QPG in [("7b_mha", 4096, 1, 32, 1), ("70b_gqa_tp4", 4096, 1, 2, 8),
+                               ("falcon40b_tp8", 2048, 1, 1, 16)]:
+        HN = 128
+        qkv = torch.randn(S, B, G, QPG + 2, HN, device="cuda").bfloat16()
+        dout = torch.randn(S, B, G * QPG * HN, device="cuda").bfloat16()
+        scale = 1 / math.sqrt(HN)
+        out, lse = SC.attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, True)
+        dqkv = torch.empty_like(qkv)
+        fl = 10.0 * S * S * G * QPG * HN * B / 2     # 5 GEMMs of the single-pass formulation
+        t_own = timeit(lambda: Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, True))
+        rec = dict(kernel="attn_bwd", shape=name, S=S, heads=G * QPG, kv_heads=G, ms_own=t_own,
+                   tflops_own_5gemm_equiv=fl / t_own / 1e9)
+        try:
+            k = qkv[:, :, :, QPG].permute(1, 0, 2, 3)
+            v = qkv[:, :, :, QPG + 1].permute(1, 0, 2, 3)
+            q = qkv[:, :, :, :QPG].reshape(S, B, G * QPG, HN).permute(1, 0, 2, 3)
+            o4 = out.view(S, B, G * QPG, HN).permute(1, 0, 2, 3)
+            do4 = dout.view(S, B, G * QPG, HN).permute(1, 0, 2, 3)
+            dq = torch.empty(B, S, G * QPG, HN, device="cuda", dtype=torch.bfloat16)
+            dk = torch.empty(B, S, G, HN, device="cuda", dtype=torch.bfloat16)
+            dv = torch.empty_like(dk)
+            t_fa = timeit(lambda: Fn._fa2_backward(do4, q, k, v, o4, lse, dq, dk, dv, scale, True))
+            rec.update(ms_fa2=t_fa, tflops_fa2=fl / t_fa / 1e9)
+        except Exception as e:  # noqa: BLE001
+            rec.update(fa2_error=str(e)[:200])
+        report(**rec)
+
+
 def bench_norm():
     M, H = 4096, 4096
     x = torch.randn(M, H, device="cuda").bfloat16()
@@ -196,7 +226,7 @@ def bench_adam():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["gemm", "attn", "norm", "elementwise", "adam"]
+    which = sys.argv[1:] or ["gemm", "attn", "attn_bwd", "norm", "elementwise", "adam"]
     for w in which:
         try:
             globals()["bench_" + w]()

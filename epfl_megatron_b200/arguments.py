@@ -173,6 +173,7 @@ _GROUPS = {
             "BertWordPieceLowerCase", "BertWordPieceCase", "GPT2BPETokenizer",
             "SentencePieceTokenizer", "FalconTokenizer", "NullTokenizer"])),
         ("--tokenizer_model", dict(type=str)),
+        ("--vocab_size", dict(type=int, default=None)),   # NullTokenizer only (synthetic data)
         ("--no_new_tokens", dict(action=F, dest="new_tokens")),
         ("--data_impl", dict(type=str, default="infer", choices=["lazy", "cached", "mmap", "infer"])),
         ("--reset_position_ids", dict(action=T)), ("--reset_attention_mask", dict(action=T)),

@@ -439,7 +439,20 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+// cuTensorMapEncodeTiled is a DRIVER entry point: unlike runtime calls it does not bind the
+// device's primary context to the calling thread. A thread whose first CUDA action is one of
+// our launches (an autograd worker starting a pipeline stage's backward with a GEMM) would get
+// CUDA_ERROR_INVALID_CONTEXT from the encode, so bind the context once per thread first.
+void ensure_thread_context() {
+  static thread_local bool bound = false;
+  if (!bound) {
+    cudaFree(nullptr);
+    bound = true;
+  }
+}
+
 EncodeTiledFn get_encode_fn() {
+  ensure_thread_context();
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {

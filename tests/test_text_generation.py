@@ -1,0 +1,65 @@
+"""Text generation on CPU: sampling filters, beam pool, and (in a subprocess that owns the
+global args) KV-cache decoding vs un-cached recomputation, scoring, beam search, REST server."""
+import json
+import os
+import subprocess
+import sys
+
+import torch
+
+from epfl_megatron_b200.text_generation.beam_utils import BeamHypotheses
+from epfl_megatron_b200.text_generation.sampling import (modify_logits_for_top_k_filtering,
+                                                         modify_logits_for_top_p_filtering, sample)
+from epfl_megatron_b200.text_generation_server import validate_request
+from tests.helpers.launch import free_port
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_top_k_top_p_filters():
+    logits = torch.tensor([[1.0, 3.0, 2.0, 0.0], [0.5, 0.1, 0.2, 4.0]])
+    a = logits.clone()
+    modify_logits_for_top_k_filtering(a, 2)
+    assert torch.isinf(a[0, 0]) and torch.isinf(a[0, 3]) and a[0, 1] == 3.0 and a[0, 2] == 2.0
+    b = logits.clone()
+    modify_logits_for_top_p_filtering(b, 0.5)
+    assert b[0, 1] == 3.0 and torch.isinf(b[0, 3])       # the top token always survives
+    assert b[1, 3] == 4.0 and torch.isinf(b[1, 0])
+    assert sample(logits, top_k=1).tolist() == [1, 3]
+    torch.manual_seed(0)
+    s = sample(logits, top_k=2, temperature=0.7)
+    assert s[0] in (1, 2) and s[1] in (0, 3)
+    assert int(sample(torch.tensor([[0.0, 0.0, 9.0]]), top_k=1, vocab_size=2)) == 1   # clamp to vocab
+
+
+def test_beam_hypotheses():
+    h = BeamHypotheses(2, length_penalty=1.0)
+    h.add("a", -4.0, 4)
+    h.add("b", -2.0, 4)
+    h.add("c", -8.0, 4)          # worse than both: dropped
+    assert sorted(x[1] for x in h.beams) == ["a", "b"]
+    assert h.is_done(-6.0, 4) and not h.is_done(-1.0, 4)
+
+
+def test_request_validation():
+    assert validate_request({})[1] == "prompts argument required"
+    assert validate_request({"prompts": ["x"], "top_k": 5, "top_p": 0.5})[1].startswith("cannot set both")
+    assert validate_request({"prompts": [""], "tokens_to_generate": 2})[1] == "Empty prompts require add_BOS=true"
+    assert validate_request({"prompts": ["a", "b"], "beam_width": 2})[1].startswith("When doing beam_search")
+    p, err = validate_request({"prompts": ["a"], "tokens_to_generate": 5, "top_p": 0.9, "top_p_decay": 0.5})
+    assert err is None and p["top_p_decay"] == 0.5 and p["tokens_to_generate"] == 5
+    assert validate_request({"prompts": ["a"], "tokens_to_generate": 0})[1].startswith("tokens_to_generate=0")
+
+
+def test_generation_end_to_end_cpu():
+    env = dict(os.environ, MASTER_PORT=str(free_port()), GEN_TEST_PORT=str(free_port()),
+               B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "helpers", "gen_worker.py")],
+                       capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("RESULT ")]
+    assert r.returncode == 0 and lines, r.stdout[-2000:] + r.stderr[-4000:]
+    out = json.loads(lines[-1][7:])
+    assert out["shape"] == [2, 13]
+    for k in ("greedy_matches_uncached", "logprobs_finite", "sampled_texts", "score_shape_ok", "beam_ok",
+              "server_ok", "server_rejects", "server_beam"):
+        assert out[k], (k, out)

@@ -421,7 +421,10 @@ def _get_num_layers(args, is_encoder_and_decoder_model, is_decoder=False):
             n = 0 if args.standalone_embedding_stage and mpu.get_pipeline_model_parallel_rank() == 0 \
                 else args.num_layers // args.transformer_pipeline_model_parallel_size
     else:
-        n = args.decoder_num_layers if is_decoder else args.encoder_num_layers
+        # the reference leaves decoder_num_layers unset unless the flag is given (its T5 recipes
+        # only pass --num_layers); an unset value means "as deep as the encoder"
+        dec = args.decoder_num_layers if args.decoder_num_layers is not None else args.encoder_num_layers
+        n = dec if is_decoder else args.encoder_num_layers
     return n
 
 

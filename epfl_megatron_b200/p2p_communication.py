@@ -56,6 +56,12 @@ def _communicate(tensor_send_next, tensor_send_prev, recv_prev, recv_next, tenso
     """Send to / receive from the neighbouring pipeline stages in one batched call."""
     args = args or global_vars.get_args()
     tensor_recv_prev = tensor_recv_next = None
+    if tensor_shape is None:
+        # activation shape between stages: [s (/tp under sequence parallelism), micro batch, h]
+        s = args.seq_length
+        if args.sequence_parallel:
+            s //= mpu.get_tensor_model_parallel_world_size()
+        tensor_shape = (s, args.micro_batch_size, args.hidden_size)
     if not args.variable_seq_lengths:
         recv_prev_shape = recv_next_shape = tensor_shape
     else:

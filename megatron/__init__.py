@@ -38,9 +38,19 @@ _ALIASES = {
     "data.t5_dataset": "data.t5_dataset", "data.ict_dataset": "data.ict_dataset",
     "tokenizer": "tokenizer", "tokenizer.tokenizer": "tokenizer.tokenizer",
     "text_generation": "text_generation", "text_generation.api": "text_generation.api",
-    "text_generation.generation": "text_generation.generation",
-    "text_generation.forward_step": "text_generation.forward_step",
+    "text_generation.generation": "text_generation.engine",
+    "text_generation.forward_step": "text_generation.engine",
+    "text_generation.sampling": "text_generation.sampling",
+    "text_generation.tokenization": "text_generation.tokenization",
+    "text_generation.communication": "text_generation.communication",
+    "text_generation.beam_utils": "text_generation.beam_utils",
     "text_generation_server": "text_generation_server",
+    "data.realm_index": "data.realm_index", "data.realm_dataset_utils": "data.realm_dataset_utils",
+    "data.biencoder_dataset_utils": "data.biencoder_dataset_utils",
+    "data.orqa_wiki_dataset": "data.orqa_wiki_dataset", "data.helpers": "data.helpers",
+    "tokenizer.bert_tokenization": "tokenizer.bert_tokenization",
+    "tokenizer.gpt2_tokenization": "tokenizer.gpt2_tokenization",
+    "indexer": "indexer",
 }
 
 

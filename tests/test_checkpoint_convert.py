@@ -139,3 +139,42 @@ def test_permute_qkv_is_an_involution_pair():
     hn, qpg = 16, 4
     g = w.view(2, qpg + 2, hn, 128)
     assert torch.equal(there.view(2, qpg + 2, hn, 128)[:, qpg + 1], g[:, qpg + 1])   # v untouched
+
+
+def test_loader_saver_plugins_match_direct_reshard(tmp_path):
+    """The queue protocol (loader plug-in -> saver plug-in) writes the same shards as the
+    direct file-level path of tools/checkpoint_util.py."""
+    import queue as pyqueue
+    import types
+    import weights2megatron as w2m
+    sys.path.insert(0, ROOT)
+    from tools import checkpoint_loader_megatron as loader, checkpoint_saver_megatron as saver
+    hf, cfg = _tiny_hf_llama(2)
+    mega = tmp_path / "mega"
+    w2m.convert("llama2", 7, mega, dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    direct, via_queue = tmp_path / "direct", tmp_path / "queue"
+    _run(["tools/checkpoint_util.py", "--model_type", "llama2", "--load_dir", str(mega), "--save_dir", str(direct),
+          "--target_tensor_parallel_size", "2", "--target_pipeline_parallel_size", "2"])
+    q = pyqueue.Queue()
+    a = types.SimpleNamespace(model_type="llama2", load_dir=str(mega), save_dir=str(via_queue), checking=True,
+                              true_vocab_size=None, target_tensor_parallel_size=2,
+                              target_pipeline_parallel_size=2)
+    loader.load_checkpoint(q, a)
+    saver.save_checkpoint(q, a)
+    for t in range(2):
+        for p in range(2):
+            d = torch.load(direct / "release" / f"mp_rank_{t:02d}_{p:03d}" / "model_optim_rng.pt", weights_only=False)
+            v = torch.load(via_queue / "release" / f"mp_rank_{t:02d}_{p:03d}" / "model_optim_rng.pt", weights_only=False)
+
+            def flat(x, pre=""):
+                out = {}
+                for k, val in x.items():
+                    if isinstance(val, dict):
+                        out.update(flat(val, pre + k + "/"))
+                    else:
+                        out[pre + k] = val
+                return out
+            fd, fv = flat(d["model"]), flat(v["model"])
+            assert fd.keys() == fv.keys()
+            for k in fd:
+                assert torch.equal(fd[k], fv[k]), k

@@ -47,7 +47,7 @@ def build_arg_list(a, tp, dp):
         L = a.debug_layers
     gbs = a.micro_batch * a.num_microbatches * dp
     argv = [
-        "--b200_kernels", getattr(a, 'kernels', 'auto'),
+        "--b200_kernels", getattr(a, 'kernels', 'auto'), "--b200_fused_comm", getattr(a, 'fused_comm', 'auto'),
         "--model_name", "llama2", "--num_layers", str(L), "--hidden_size", str(h),
         "--num_attention_heads", str(nh), "--num_attention_heads_kv", str(nkv),
         "--ffn_hidden_size", str(ffn), "--seq_length", str(a.seq), "--max_position_embeddings", str(a.seq),
@@ -286,6 +286,7 @@ def main():
     p.add_argument("--verbose", action="store_true")
     p.add_argument("--debug_layers", type=int, default=0, help="debug only: override the layer count")
     p.add_argument("--kernels", default="auto", help="debug only: auto|off")
+    p.add_argument("--fused_comm", default="auto", help="A/B only: auto|on|off (in-kernel TP collectives)")
     p.add_argument("--profile", action="store_true", help="1 warm-up + K steps, no e2e region; for ncu, NOT a bench value")
     a = p.parse_args()
     if a.warmup < 3 and not a.profile:

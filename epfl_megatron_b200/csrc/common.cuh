@@ -139,9 +139,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // hanging the GPU until the watchdog.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
+  long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 26)) {
-      asm volatile("trap;");
+    // time-based bound (~20 s): kernels that overlap a cross-GPU transfer may legitimately
+    // wait for a peer that started late
+    if ((++spins & 0xFFFFu) == 0) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > 40000000000LL) asm volatile("trap;");
     }
   }
 }

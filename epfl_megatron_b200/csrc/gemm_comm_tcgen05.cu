@@ -1,0 +1,558 @@
+// Tensor-parallel GEMMs with the collective INSIDE the kernel (K8 / K9 of SURVEY.md section 8),
+// over peer-mapped ("symmetric") memory of the GPUs of one NVSwitch domain.
+//
+//   mode AG  (all-gather -> GEMM): ColumnParallelLinear forward under sequence parallelism and
+//     the dgrad of RowParallelLinear (megatron/core/tensor_parallel/layers.py:225-243 and
+//     mappings.py:244-246 + the matmul behind them).  C[M, N] = gather_rows(X)[M, K] * B^T.
+//     Every CTA donates one warp that PULLS the other ranks' row chunks out of their staging
+//     buffers (16-byte peer loads over NVLink) into the local gathered matrix, 128-row block
+//     by 128-row block; a counter per block is bumped when a warp's share has landed. The
+//     TMA producers walk the output tiles starting with the rank's own chunk and only wait
+//     on a block's counter right before its first A tile is loaded, so the transfer of chunk
+//     r+1 runs under the MMAs of chunk r. The gathered matrix is an ordinary tensor the
+//     caller keeps for the weight gradient (no second gather in backward).
+//   mode RS  (GEMM -> reduce-scatter): RowParallelLinear forward and the dgrad of
+//     ColumnParallelLinear (layers.py:691-692, :285-296).  out[M/tp, N] = sum_r (A_r B_r^T)[chunk].
+//     The epilogue converts each accumulator tile to bf16 and STORES it straight into the
+//     owning rank's slot for this source (peer stores), tiles owned by other ranks first;
+//     one warp-level release-add per tile quarter tells the owner. When a CTA has run out of
+//     tiles its epilogue warps reduce 8-row strips of the rank's own chunk (fp32 sum of the tp
+//     bf16 partials in rank order, so every rank computes the same bits) as soon as the
+//     strip's counters show all tp contributions.
+//
+// Protocol state lives in the symmetric workspace (csrc/comm.cu): monotonic u32 counters
+// compared with wrap-around arithmetic, one epoch per call. Waits on other GPUs are bounded
+// (trap after ~5 s) so a protocol bug surfaces as a launch error instead of a hung device.
+// The MMA pipeline is the CTA-pair kernel of gemm_tcgen05.cu (cta_group::2, 256 x 256 tiles).
+#include "common.cuh"
+
+namespace b200 {
+
+int make_tmap_2d(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
+                 int box_rows);
+
+namespace fc {
+
+constexpr int kBM = 128, kBK = 64, kStages = 5, kBN = 256, kHalfN = 128, kThreads = 256, kGroupM = 8;
+constexpr int kABytes = kBM * kBK * 2, kBBytes = kHalfN * kBK * 2, kStageBytes = kABytes + kBBytes;
+constexpr int kOutBoxBytes = kBM * 128;                       // [128 rows x 64 bf16], 128B swizzle
+constexpr int kOutOffset = kStages * kStageBytes;             // 4 boxes = the CTA's 128 x 256 tile
+constexpr int kBarOffset = kOutOffset + 4 * kOutBoxBytes, kSmemTotal = kBarOffset + 256 + 1024;
+constexpr int kMaxTP = 8;
+constexpr int kModeAG = 1, kModeRS = 2;
+
+struct CommArgs {
+  // TMA store maps: [0] = C (AG mode) or, in RS mode, [o] = owner o's slot for source <me>
+  alignas(64) CUtensorMap out_map[kMaxTP];
+  int mode, tp, rank, rows_per_chunk;
+  unsigned epoch;
+  // ---- all-gather ----
+  const uint4* peer_src[kMaxTP];     // rank r's staging shard [rows_per_chunk, K]
+  uint4* gathered;                   // local [M, K]
+  unsigned* row_ready;               // [M / 128] warps that delivered their share of a row block
+  unsigned* row_ready_next;          // the other counter set: zeroed here for the next call
+  const unsigned* shard_ready;       // [tp] epoch at which rank r's staging shard became valid
+  unsigned* chunk_done;              // [tp] warps that finished pulling chunk r
+  unsigned* chunk_done_next;
+  int max_blocks;
+  unsigned* peer_consumed[kMaxTP];   // rank r's "rank <me> has pulled my shard" flag
+  long long row_bytes;
+  // ---- reduce-scatter ----
+  unsigned* cnt_dst[kMaxTP];         // owner o's arrival counters [rows_per_chunk / 128]
+  const __nv_bfloat16* my_parts;     // my slots [tp][rows_per_chunk][N]
+  const unsigned* my_cnt;
+  unsigned rs_target;                // arrivals per row block in this call (counters start at 0)
+  __nv_bfloat16* out;                // [rows_per_chunk, N]
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_sys_add(unsigned* p, unsigned v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void red_release_gpu_add(unsigned* p, unsigned v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_global() {
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+// wrap-safe "counter has reached target"
+__device__ __forceinline__ bool reached(unsigned v, unsigned target) {
+  return static_cast<int>(v - target) >= 0;
+}
+// First wait that timed out: {site, blockIdx, value seen, target, epoch, mode, rank, index}.
+// A timed-out wait is recorded and then abandoned (the result of that call is garbage, the host
+// checks b200_comm_debug_read in debug / test runs); the GPU is never left spinning.
+__device__ unsigned g_comm_debug[8];
+
+template <bool kSys>
+__device__ __forceinline__ void spin_until(const unsigned* p, unsigned target, unsigned site,
+                                           unsigned index, unsigned epoch, int mode, int rank) {
+  const long long t0 = clock64();
+  unsigned v;
+  while (!reached(v = (kSys ? ld_acquire_sys(p) : ld_acquire_gpu(p)), target)) {
+    __nanosleep(64);
+    if (clock64() - t0 > 4000000000LL) {
+      if (atomicCAS(&g_comm_debug[0], 0u, site) == 0u) {
+        g_comm_debug[1] = blockIdx.x;
+        g_comm_debug[2] = v;
+        g_comm_debug[3] = target;
+        g_comm_debug[4] = epoch;
+        g_comm_debug[5] = (unsigned)mode;
+        g_comm_debug[6] = (unsigned)rank;
+        g_comm_debug[7] = index;
+      }
+      return;
+    }
+  }
+}
+
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& tm, int& tn) {
+  const int group = kGroupM * tiles_n;
+  const int gid = tile / group;
+  const int first_m = gid * kGroupM;
+  const int gsz = min(tiles_m - first_m, kGroupM);
+  const int in_group = tile - gid * group;
+  tm = first_m + in_group % gsz;
+  tn = in_group / gsz;
+}
+
+template <bool kBMN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 __nv_bfloat16* __restrict__ Cout, int M, int N, int K, long long ldc,
+                 const __grid_constant__ CommArgs ca) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kBarOffset);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const int tiles_m = (M + 2 * kBM - 1) / (2 * kBM);
+  const int tiles_n = (N + kBN - 1) / kBN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + kBK - 1) / kBK;
+  const int tiles_per_chunk = ca.rows_per_chunk / (2 * kBM);
+  // AG: start with the rank's own rows; RS: finish with them
+  const int tm_rot = (ca.mode == kModeAG ? ca.rank : (ca.rank + 1) % ca.tp) * tiles_per_chunk;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 8);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc_pair<2 * kBN>(tmem_slot);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------ TMA producer (both CTAs) ------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const unsigned ready_target = 2 * gridDim.x;   // two copier warps per CTA, counters start at 0
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int tm, tn;
+        tile_coords(tile, tiles_m, tiles_n, tm, tn);
+        tm = (tm + tm_rot) % tiles_m;
+        const int m0 = tm * 2 * kBM + static_cast<int>(crank) * kBM;
+        const int n0 = tn * kBN + static_cast<int>(crank) * kHalfN;
+        if (ca.mode == kModeAG && m0 < M && m0 / ca.rows_per_chunk != ca.rank) {
+          // rows pulled from another GPU by the copier warps: wait for this 128-row block
+          spin_until<false>(&ca.row_ready[m0 / kBM], ready_target, 1u, m0 / kBM, ca.epoch, ca.mode, ca.rank);
+          fence_proxy_async_global();
+        }
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * kStageBytes;
+          uint8_t* sb = sa + kABytes;
+          if (crank == 0) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
+          tma_load_2d_pair(sa, &tmA, &full_bar[stage], kb * kBK, m0);
+          if (!kBMN) {
+            tma_load_2d_pair(sb, &tmB, &full_bar[stage], kb * kBK, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < kHalfN / 64; ++j)
+              tma_load_2d_pair(sb + j * (kBK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * kBK);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------ MMA issuer (leader CTA only) --------------
+    if (lane == 0 && crank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * kBM, kBN, 0, kBMN ? 1 : 0);
+      constexpr uint32_t lbo_b = kBMN ? kBK * 128 : 16;
+      constexpr uint32_t kstep_b = kBMN ? 16 * 128 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * kBN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+          const uint32_t sb = sa + kABytes;
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            const uint64_t da = make_sw128_desc(sa + k * 32, 16, 1024);
+            const uint64_t db = make_sw128_desc(sb + k * kstep_b, lbo_b, 1024);
+            umma_bf16_ss_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_pair(&empty_bar[stage]);
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit_pair(&tmem_full[as]);
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 2 || warp == 3) {
+    // ------------------------------ all-gather copiers ------------------------
+    if (ca.mode == kModeAG) {
+      const int nw = 2 * gridDim.x, w = 2 * blockIdx.x + (warp - 2);
+      if (w == 0) {   // nobody reads the other counter set during this call: clear it for the next
+        for (int i = lane; i < ca.max_blocks; i += 32) ca.row_ready_next[i] = 0u;
+        if (lane < kMaxTP) ca.chunk_done_next[lane] = 0u;
+      }
+      const long long segs_per_block = (long long)kBM * (ca.row_bytes / 512);  // 512 B = one warp access
+      const int nrb = ca.rows_per_chunk / kBM;
+      for (int step = 1; step < ca.tp; ++step) {
+        const int src = (ca.rank + step) % ca.tp;
+        if (lane == 0) spin_until<true>(&ca.shard_ready[src], ca.epoch, 2u, src, ca.epoch, ca.mode, ca.rank);
+        __syncwarp();
+        const uint4* s = ca.peer_src[src] + lane;
+        uint4* d = ca.gathered + (long long)src * ca.rows_per_chunk * (ca.row_bytes / 16) + lane;
+        for (int rb = 0; rb < nrb; ++rb) {
+          const long long base = (long long)rb * segs_per_block;
+          constexpr int U = 16;   // 16 x 512 B per warp in flight: ~2.4 MB over the whole grid
+          for (long long sg = w; sg < segs_per_block; sg += (long long)nw * U) {
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const long long g = sg + (long long)u * nw;
+              if (g < segs_per_block) v[u] = __ldcv(s + (base + g) * 32);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+              const long long g = sg + (long long)u * nw;
+              if (g < segs_per_block) d[(base + g) * 32] = v[u];
+            }
+          }
+          fence_proxy_async_global();   // the rows are read back by TMA (async proxy)
+          __syncwarp();
+          if (lane == 0) red_release_gpu_add(&ca.row_ready[src * nrb + rb], 1u);
+        }
+        if (lane == 0) {
+          __threadfence();
+          const unsigned old = atomicAdd(&ca.chunk_done[src], 1u);
+          if (old + 1u == (unsigned)nw) st_release_sys(ca.peer_consumed[src], ca.epoch);
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ------------------------------ epilogue (both CTAs) ----------------------
+    // TMEM -> registers -> bf16 -> swizzled shared-memory boxes -> TMA store (to the local C or
+    // straight into the owning rank's partial-sum slot over NVLink: full 128-byte lines).
+    const int ew = warp - 4;
+    const int r = ew * 32 + lane;     // row inside the CTA's 128-row half tile == TMEM lane
+    int as = 0;
+    uint32_t aphase = 0;
+    const uint32_t leader_empty0 = mapa_u32(smem_u32(&tmem_empty[0]), 0);
+    uint8_t* stage_out = smem + kOutOffset;
+    const bool issuer = (ew == 0 && lane == 0);
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      int tm, tn;
+      tile_coords(tile, tiles_m, tiles_n, tm, tn);
+      tm = (tm + tm_rot) % tiles_m;
+      const int row0 = tm * 2 * kBM + static_cast<int>(crank) * kBM;
+      const int n0 = tn * kBN;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      if (issuer) tma_store_wait_read<0>();          // the previous tile's boxes have been read
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN;
+#pragma unroll 1
+      for (int c = 0; c < kBN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c * 32, v);
+        tmem_ld_wait();
+        uint8_t* box = stage_out + (c >> 1) * kOutBoxBytes;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 o;
+          o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+          o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+          o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+          o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+          *reinterpret_cast<uint4*>(box + sw128_offset(r, (c & 1) * 4 + q)) = o;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(leader_empty0 + as * 8);   // TMEM stage free for the MMAs
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (issuer && row0 < M) {
+        int owner = 0, drow = row0;
+        if (ca.mode == kModeRS) {
+          owner = row0 / ca.rows_per_chunk;
+          drow = row0 - owner * ca.rows_per_chunk;
+        }
+        const CUtensorMap* om = &ca.out_map[ca.mode == kModeRS ? owner : 0];
+#pragma unroll
+        for (int bx = 0; bx < 4; ++bx)
+          if (n0 + bx * 64 < N) tma_store_2d(om, stage_out + bx * kOutBoxBytes, n0 + bx * 64, drow);
+        tma_store_commit();
+        if (ca.mode == kModeRS) {
+          tma_store_wait<0>();              // the partial rows have been written ...
+          fence_proxy_async_global();
+          __threadfence_system();           // ... and are visible before the owner counts them
+          red_release_sys_add(ca.cnt_dst[owner] + drow / kBM, 1u);
+        }
+      }
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+    if (issuer) tma_store_wait<0>();
+  }
+
+  if (ca.mode == kModeRS) {
+    // ------------------------------ reduce own chunk --------------------------
+    // All 8 warps join once their role loop is over (lanes that had no role get here first
+    // and meet their warp's lane 0 at the __syncwarp below). A unit is an 8-row strip; the
+    // strip is summed as soon as its 128-row block has received every rank's tile pieces.
+    const unsigned target = ca.rs_target;
+    const int units = ca.rows_per_chunk / 8;
+    const int vec_per_row = N / 8;
+    const int vecs = 8 * vec_per_row;
+    const size_t slot = (size_t)ca.rows_per_chunk * N;
+    for (int unit = blockIdx.x; unit < units; unit += gridDim.x) {
+      const int r0 = unit * 8;
+      if (lane == 0) spin_until<true>(&ca.my_cnt[r0 / kBM], target, 3u, r0 / kBM, ca.epoch, ca.mode, ca.rank);
+      __syncwarp();
+      const size_t base = (size_t)r0 * N;
+      constexpr int V = 4;
+      for (int idx = threadIdx.x; idx < vecs; idx += kThreads * V) {
+        float acc[V][8];
+#pragma unroll
+        for (int u = 0; u < V; ++u)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[u][j] = 0.f;
+        for (int sidx = 0; sidx < ca.tp; ++sidx) {
+          uint4 v[V];
+#pragma unroll
+          for (int u = 0; u < V; ++u) {
+            const int id = idx + u * kThreads;
+            if (id < vecs)
+              v[u] = __ldcv(reinterpret_cast<const uint4*>(ca.my_parts + sidx * slot + base + (size_t)id * 8));
+          }
+#pragma unroll
+          for (int u = 0; u < V; ++u) {
+            float f[8];
+            unpack8(*reinterpret_cast<const bf16x8*>(&v[u]), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[u][j] += f[j];
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < V; ++u) {
+          const int id = idx + u * kThreads;
+          if (id < vecs) {
+            const bf16x8 o = pack8(acc[u]);
+            *reinterpret_cast<uint4*>(ca.out + base + (size_t)id * 8) = *reinterpret_cast<const uint4*>(&o);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair<2 * kBN>(tmem_base);
+  }
+}
+
+// bf16 [rows, cols] row stride ld: store box [128 rows x 64 cols], 128-byte swizzle
+static int make_out_map(CUtensorMap* map, void* base, long long rows, long long cols, long long ld) {
+  return make_tmap_2d(map, base, rows, cols, ld, kBM);
+}
+
+template <bool kBMN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, int K, long long ldc,
+           const CommArgs& ca, cudaStream_t stream) {
+  auto kern = gemm_comm_kernel<kBMN>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  // every CTA takes part in the collective, so the grid is always the full machine
+  kern<<<kNumSMs, kThreads, kSmemTotal, stream>>>(ta, tb, (__nv_bfloat16*)C, M, N, K, ldc, ca);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace fc
+}  // namespace b200
+
+using namespace b200;
+using b200::fc::CommArgs;
+
+// Workspace layout (all pointers are device addresses valid on THIS GPU; peer_* entries point
+// into the other ranks' workspaces through the IPC mappings of csrc/comm.cu):
+//   flags (u32): row_ready[2][max_blocks] | shard_ready[8] | chunk_done[2][8] | consumed[8] | rs_cnt[2][max_blocks]
+struct B200CommDesc {
+  int tp, rank;
+  void* peer_stage[8];        // rank r's staging shard
+  unsigned* peer_flags[8];    // rank r's flag block
+  int max_blocks;
+};
+
+static inline unsigned* f_row_ready(unsigned* f, int mb, int set) { return f + set * mb; }
+static inline unsigned* f_shard_ready(unsigned* f, int mb) { return f + 2 * mb; }
+static inline unsigned* f_chunk_done(unsigned* f, int mb, int set) { return f + 2 * mb + 8 + set * 8; }
+static inline unsigned* f_consumed(unsigned* f, int mb) { return f + 2 * mb + 24; }
+static inline unsigned* f_rs_cnt(unsigned* f, int mb, int set) { return f + 2 * mb + 32 + set * mb; }
+
+// Copies the 8-word record of the first timed-out wait on this GPU (all zero = none) and clears it.
+B200_API int b200_comm_debug_read(unsigned* out8) {
+  cudaError_t e = cudaMemcpyFromSymbol(out8, fc::g_comm_debug, 8 * sizeof(unsigned));
+  if (e != cudaSuccess) return (int)e;
+  unsigned z[8] = {};
+  return (int)cudaMemcpyToSymbol(fc::g_comm_debug, z, sizeof(z));
+}
+
+B200_API int b200_comm_flag_words(int max_blocks) { return 4 * max_blocks + 32; }
+// word offsets of the flag blocks the host side signals / waits on
+B200_API int b200_comm_shard_ready_word(int max_blocks) { return 2 * max_blocks; }
+B200_API int b200_comm_consumed_word(int max_blocks) { return 2 * max_blocks + 24; }
+
+// C[M, N] = gathered[M, K] * B^T where gathered rows [r*M/tp, (r+1)*M/tp) come from rank r's
+// staging shard (the caller has already placed its own chunk into `gathered`). epoch: 1, 2, ...
+// per call on this workspace, identical on all ranks.
+B200_API int b200_gemm_allgather(const B200CommDesc* d, void* gathered, const void* B, void* C, int M,
+                                 int N, int K, int b_mn_major, long long ldb, long long ldc,
+                                 unsigned epoch, cudaStream_t stream) {
+  if (!d || d->tp < 2 || d->tp > 8 || M % d->tp) return B200_ERR_BAD_ARG;
+  const int rpc = M / d->tp;
+  if (rpc % 256 || (K * 2) % 512 || M / 128 > d->max_blocks) return B200_ERR_UNSUPPORTED;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d(&ta, gathered, M, K, K, fc::kBM);
+  if (rc) return rc;
+  rc = b_mn_major ? make_tmap_2d(&tb, B, K, N, ldb, fc::kBK) : make_tmap_2d(&tb, B, N, K, ldb, fc::kHalfN);
+  if (rc) return rc;
+  CommArgs ca = {};
+  ca.mode = fc::kModeAG;
+  ca.tp = d->tp;
+  ca.rank = d->rank;
+  ca.rows_per_chunk = rpc;
+  ca.epoch = epoch;
+  unsigned* mine = d->peer_flags[d->rank];
+  for (int r = 0; r < d->tp; ++r) {
+    ca.peer_src[r] = (const uint4*)d->peer_stage[r];
+    ca.peer_consumed[r] = f_consumed(d->peer_flags[r], d->max_blocks) + d->rank;
+  }
+  ca.gathered = (uint4*)gathered;
+  const int set = (int)(epoch & 1u);   // per-call counters alternate; each call clears the other set
+  ca.row_ready = f_row_ready(mine, d->max_blocks, set);
+  ca.row_ready_next = f_row_ready(mine, d->max_blocks, set ^ 1);
+  ca.shard_ready = f_shard_ready(mine, d->max_blocks);
+  ca.chunk_done = f_chunk_done(mine, d->max_blocks, set);
+  ca.chunk_done_next = f_chunk_done(mine, d->max_blocks, set ^ 1);
+  ca.max_blocks = d->max_blocks;
+  ca.row_bytes = (long long)K * 2;
+  rc = fc::make_out_map(&ca.out_map[0], C, M, N, ldc);
+  if (rc) return rc;
+  return b_mn_major ? fc::launch<true>(ta, tb, C, M, N, K, ldc, ca, stream)
+                    : fc::launch<false>(ta, tb, C, M, N, K, ldc, ca, stream);
+}
+
+// Arrivals a 128-row block of the owner's counters receives in one reduce-scatter call.
+B200_API int b200_gemm_rs_arrivals(int N, int tp) { return ((N + fc::kBN - 1) / fc::kBN) * tp; }
+
+// out[M/tp, N] = rows chunk <rank> of sum over ranks of A_r[M, K] * B_r^T. The workspace has two
+// sets of partial-sum slots and arrival counters; callers alternate `set` call by call, which is
+// enough to keep a fast rank from touching state a slow rank still reads (a rank can finish call
+// e+1 only after every peer has finished call e). peer_parts[r] = rank r's slots of that set;
+// rs_target = b200_gemm_rs_arrivals(N, tp). The owner zeroes the set's counters after its kernel.
+B200_API int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int set,
+                                      const void* A, const void* B, void* out, int M, int N, int K,
+                                      int b_mn_major, long long lda, long long ldb,
+                                      unsigned rs_target, cudaStream_t stream) {
+  if (!d || d->tp < 2 || d->tp > 8 || M % d->tp || set < 0 || set > 1) return B200_ERR_BAD_ARG;
+  const int rpc = M / d->tp;
+  if (rpc % 256 || N % 8 || M / 128 > d->max_blocks || (lda % 8) || (ldb % 8)) return B200_ERR_UNSUPPORTED;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d(&ta, A, M, K, lda, fc::kBM);
+  if (rc) return rc;
+  rc = b_mn_major ? make_tmap_2d(&tb, B, K, N, ldb, fc::kBK) : make_tmap_2d(&tb, B, N, K, ldb, fc::kHalfN);
+  if (rc) return rc;
+  CommArgs ca = {};
+  ca.mode = fc::kModeRS;
+  ca.tp = d->tp;
+  ca.rank = d->rank;
+  ca.rows_per_chunk = rpc;
+  ca.rs_target = rs_target;
+  const size_t slot = (size_t)rpc * N;
+  for (int o = 0; o < d->tp; ++o) {
+    rc = fc::make_out_map(&ca.out_map[o], (__nv_bfloat16*)peer_parts[o] + slot * d->rank, rpc, N, N);
+    if (rc) return rc;
+    ca.cnt_dst[o] = f_rs_cnt(d->peer_flags[o], d->max_blocks, set);
+  }
+  ca.my_parts = (const __nv_bfloat16*)peer_parts[d->rank];
+  ca.my_cnt = f_rs_cnt(d->peer_flags[d->rank], d->max_blocks, set);
+  ca.out = (__nv_bfloat16*)out;
+  rc = b_mn_major ? fc::launch<true>(ta, tb, nullptr, M, N, K, N, ca, stream)
+                  : fc::launch<false>(ta, tb, nullptr, M, N, K, N, ca, stream);
+  if (rc) return rc;
+  // peers touch this set again two calls from now at the earliest (see above)
+  return (int)cudaMemsetAsync(const_cast<unsigned*>(ca.my_cnt), 0, sizeof(unsigned) * (rpc / 128), stream);
+}

@@ -42,6 +42,8 @@ def initialize_megatron(extra_args_provider=None, args_defaults=None, ignore_unk
     global_vars.set_global_variables(args)
     Fn.set_kernel_mode({"auto": "auto", "on": "on", "off": "off"}[args.b200_kernels])
     Fn.set_gemm_mode(args.b200_gemm)
+    from .parallel import layers as _tp_layers
+    _tp_layers.set_fused_comm_mode(args.b200_fused_comm)
     _initialize_distributed(args)
     if args.rank == 0:
         print(f"> setting random seeds to {args.seed} ...", flush=True)

@@ -234,9 +234,134 @@ class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
         return grad_input, grad_weight, grad_bias, None, None, None
 
 
+# ---------------------------------------------------------------------------------------------
+# Sequence-parallel linears with the collective inside the GEMM kernel (parallel/symm.py,
+# csrc/gemm_comm_tcgen05.cu). Same math as the class above + the mappings around it.
+# ---------------------------------------------------------------------------------------------
+_FUSED_COMM = "auto"    # auto | on | off  (--b200_fused_comm)
+
+
+def set_fused_comm_mode(mode: str):
+    global _FUSED_COMM
+    assert mode in ("auto", "on", "off")
+    _FUSED_COMM = mode
+
+
+def _fused_comm_ok(rows_local: int, k_gather: int, n_scatter: int, *tensors) -> bool:
+    """rows_local: rows of the sequence shard; k_gather: width of the gathered operand;
+    n_scatter: width of the reduce-scattered result."""
+    if _FUSED_COMM == "off" or not Fn.kernels_enabled():
+        return False
+    ok = (all(t.is_cuda and t.dtype == torch.bfloat16 for t in tensors)
+          and rows_local % 256 == 0 and k_gather % 256 == 0 and n_scatter % 8 == 0
+          and 2 <= state.get_tensor_model_parallel_world_size() <= 8)
+    if not ok and _FUSED_COMM == "on":
+        raise RuntimeError(f"--b200_fused_comm on: unsupported shape rows/rank {rows_local}, "
+                           f"gathered width {k_gather}, scattered width {n_scatter}")
+    return ok
+
+
+def _workspace(rows_total: int, k_gather: int, n_scatter: int):
+    """The group's workspace, sized once for the whole model when the global args are known
+    (every gathered / scattered activation of a decoder is [s*b, hidden])."""
+    from .symm import get_workspace
+    try:
+        from .. import global_vars
+        a = global_vars.get_args()
+        rows_total = max(rows_total, a.seq_length * a.micro_batch_size)
+        k_gather = n_scatter = max(k_gather, n_scatter, a.hidden_size)
+    except Exception:  # noqa: BLE001 - used outside a configured run (tests, tools)
+        pass
+    return get_workspace(state.get_tensor_model_parallel_group(), rows_total, k_gather, n_scatter)
+
+
+def _accumulate_wgrad(w, go2, t2, gradient_accumulation_fusion):
+    """-> grad_weight or None when it went straight into w.main_grad."""
+    main = getattr(w, "main_grad", None)
+    if gradient_accumulation_fusion and main is not None:
+        first = getattr(w, "_b200_main_grad_empty", False)
+        if Fn.wgrad_accumulate(go2, t2, main, accumulate=not first):
+            w._b200_main_grad_empty = False
+            Fn._notify_grad_ready(w)
+            return None
+    return torch.matmul(go2.t(), t2)
+
+
+class _FusedColumnSP(torch.autograd.Function):
+    """[s/tp, b, h] -> all-gather along s (in kernel) -> x W^T. Backward: dgrad GEMM with the
+    reduce-scatter in its epilogue; wgrad from the gathered input kept from forward (the
+    reference gathers it a second time, layers.py:255-270, to save the memory)."""
+
+    @staticmethod
+    def forward(ctx, input, weight, gradient_accumulation_fusion):
+        s_local, b, K = input.shape
+        x2 = input.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        tp = state.get_tensor_model_parallel_world_size()
+        ws = _workspace(x2.shape[0] * tp, K, K)
+        out, gathered = ws.allgather_gemm(x2, weight)
+        ctx.save_for_backward(gathered, weight)
+        ctx.weight_ref = weight
+        ctx.gaf = gradient_accumulation_fusion
+        ctx.in_shape = input.shape
+        return out.view(s_local * tp, b, weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        gathered, weight = ctx.saved_tensors
+        N = grad_output.shape[-1]
+        go2 = grad_output.reshape(-1, N)
+        if not go2.is_contiguous():
+            go2 = go2.contiguous()
+        K = weight.shape[1]
+        ws = _workspace(go2.shape[0], K, K)
+        dx = ws.gemm_reduce_scatter(go2, weight, b_mn_major=True)        # [M/tp, K]
+        gw = _accumulate_wgrad(ctx.weight_ref, go2, gathered, ctx.gaf)
+        return dx.view(ctx.in_shape), gw, None
+
+
+class _FusedRowSP(torch.autograd.Function):
+    """[s, b, k/tp] -> x W^T with the reduce-scatter along s in the GEMM epilogue -> [s/tp, b, h].
+    Backward: the all-gather of dY feeds the dgrad GEMM from inside the kernel and the gathered
+    dY is reused for the wgrad."""
+
+    @staticmethod
+    def forward(ctx, input, weight, gradient_accumulation_fusion):
+        s, b, K = input.shape
+        x2 = input.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        tp = state.get_tensor_model_parallel_world_size()
+        N = weight.shape[0]
+        ws = _workspace(x2.shape[0], N, N)
+        out = ws.gemm_reduce_scatter(x2, weight)                          # [M/tp, N]
+        ctx.save_for_backward(x2, weight)
+        ctx.weight_ref = weight
+        ctx.gaf = gradient_accumulation_fusion
+        ctx.in_shape = input.shape
+        return out.view(s // tp, b, N)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        x2, weight = ctx.saved_tensors
+        N = grad_output.shape[-1]
+        dy2 = grad_output.reshape(-1, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        ws = _workspace(x2.shape[0], N, N)
+        dx, gathered_dy = ws.allgather_gemm(dy2, weight, b_mn_major=True)  # [M, K/tp], [M, N]
+        gw = _accumulate_wgrad(ctx.weight_ref, gathered_dy, x2, ctx.gaf)
+        return dx.view(ctx.in_shape), gw, None
+
+
 def linear_with_grad_accumulation_and_async_allreduce(input, weight, bias, gradient_accumulation_fusion,
                                                       async_grad_allreduce,
                                                       sequence_parallel_enabled):
+    if sequence_parallel_enabled and input.dim() == 3 and \
+            _fused_comm_ok(input.shape[0] * input.shape[1], input.shape[2], input.shape[2], input, weight):
+        out = _FusedColumnSP.apply(input, weight, gradient_accumulation_fusion)
+        return out + bias if bias is not None else out
     return LinearWithGradAccumulationAndAsyncCommunication.apply(
         input, weight, bias, gradient_accumulation_fusion, async_grad_allreduce,
         sequence_parallel_enabled)
@@ -344,6 +469,13 @@ class RowParallelLinear(torch.nn.Module):
         else:
             assert not self.sequence_parallel_enabled
             x = scatter_to_tensor_model_parallel_region(input_)
+        if self.sequence_parallel_enabled and x.dim() == 3 and x.shape[0] % self.world_size == 0 and \
+                _fused_comm_ok(x.shape[0] * x.shape[1] // self.world_size, self.output_size, self.output_size,
+                               x, self.weight):
+            out_ = _FusedRowSP.apply(x, self.weight, self.gradient_accumulation_fusion)
+            if not self.skip_bias_add:
+                return (out_ + self.bias if self.bias is not None else out_), None
+            return out_, self.bias
         out_parallel = linear_with_grad_accumulation_and_async_allreduce(
             x, self.weight, None, self.gradient_accumulation_fusion, False, False)
         if self.sequence_parallel_enabled:

@@ -1,0 +1,187 @@
+"""Peer-mapped workspace of one tensor-parallel group and the two fused collective GEMMs on it.
+
+Every rank of the group owns one region (csrc/comm.cu: cudaMalloc + CUDA IPC export), laid out as
+
+    flags | 2 staging shards [rows_per_chunk, K] | 2 sets of partial-sum slots [tp][rows_per_chunk][N]
+
+and maps the regions of its peers. ``allgather_gemm`` and ``gemm_reduce_scatter`` launch ONE
+kernel each (csrc/gemm_comm_tcgen05.cu) that moves activation rows over NVLink from inside the
+GEMM: they replace the all-gather + matmul of ColumnParallelLinear and the matmul +
+reduce-scatter of RowParallelLinear under sequence parallelism
+(megatron/core/tensor_parallel/layers.py:225-243, :691-692; mappings.py:89-124).
+
+Ordering rules the callers rely on (all ranks make the same calls in the same order):
+* staging shard i is rewritten at call e only after every peer reported having pulled call e-2;
+* reduce-scatter calls alternate between two slot/counter sets.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from ..ops import lib as L
+
+
+class _Desc(C.Structure):
+    _fields_ = [("tp", C.c_int), ("rank", C.c_int), ("peer_stage", C.c_void_p * 8),
+                ("peer_flags", C.c_void_p * 8), ("max_blocks", C.c_int)]
+
+
+def _wrap(ptr: int, nbytes: int, device) -> torch.Tensor:
+    """uint8 tensor over raw device memory owned by the workspace."""
+    class _Mem:
+        __cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3,
+                                    "strides": None}
+    return torch.as_tensor(_Mem(), device=device)
+
+
+class TPWorkspace:
+    """max_rows: largest M (= s*b) of a gathered activation; max_k / max_n: widest gathered input /
+    reduce-scattered output in elements."""
+
+    def __init__(self, group, max_rows: int, max_k: int, max_n: int):
+        self.group = group
+        self.tp = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        assert 2 <= self.tp <= 8
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        lib = L.lib()
+        self.max_rows, self.max_k, self.max_n = max_rows, max_k, max_n
+        self.max_blocks = (max_rows + 127) // 128
+        rpc = max_rows // self.tp
+        words = lib.b200_comm_flag_words(self.max_blocks)
+        self.w_ready = lib.b200_comm_shard_ready_word(self.max_blocks)
+        self.w_consumed = lib.b200_comm_consumed_word(self.max_blocks)
+        self.w_stage_done = words            # one extra word: completion counter of the staging kernel
+        self.flag_bytes = ((words + 1) * 4 + 4095) // 4096 * 4096
+        self.stage_bytes = (rpc * max_k * 2 + 4095) // 4096 * 4096
+        self.parts_bytes = (self.tp * rpc * max_n * 2 + 4095) // 4096 * 4096
+        self.nbytes = self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes
+        base = C.c_void_p()
+        L.call("b200_symm_alloc", self.nbytes, C.byref(base), launches=0)
+        self.base = base.value
+        handle = (C.c_ubyte * 64)()
+        L.call("b200_symm_export", self.base, handle, launches=0)
+        mine = bytes(handle)
+        handles = [None] * self.tp
+        dist.all_gather_object(handles, mine, group=group)
+        self.peer_base = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.peer_base.append(self.base)
+                continue
+            p = C.c_void_p()
+            buf = (C.c_ubyte * 64).from_buffer_copy(h)
+            L.call("b200_symm_import", buf, C.byref(p), launches=0)
+            self.peer_base.append(p.value)
+        dist.barrier(group=group)
+        self.ag_epoch = 0
+        self.rs_calls = 0
+        self._descs = [self._make_desc(i) for i in range(2)]
+        self._flags = _wrap(self.base, self.flag_bytes, self.device).view(torch.int32)
+
+    # ---- addresses -------------------------------------------------------------------------
+    def _stage(self, r, i):
+        return self.peer_base[r] + self.flag_bytes + i * self.stage_bytes
+
+    def _parts(self, r, s):
+        return self.peer_base[r] + self.flag_bytes + 2 * self.stage_bytes + s * self.parts_bytes
+
+    def _flag(self, r, word):
+        return self.peer_base[r] + 4 * word
+
+    def _make_desc(self, stage):
+        d = _Desc()
+        d.tp, d.rank, d.max_blocks = self.tp, self.rank, self.max_blocks
+        for r in range(self.tp):
+            d.peer_stage[r] = self._stage(r, stage)
+            d.peer_flags[r] = self.peer_base[r]
+        return d
+
+    # ---- all-gather -> GEMM ----------------------------------------------------------------
+    def allgather_gemm(self, x_shard: torch.Tensor, weight: torch.Tensor, b_mn_major: bool = False):
+        """x_shard [M/tp, K] (this rank's rows), weight [N, K] (or [K, N] when b_mn_major).
+        Returns (out [M, N], gathered [M, K]); ``gathered`` is a fresh tensor the caller may keep."""
+        rpc, K = x_shard.shape
+        M = rpc * self.tp
+        N = weight.shape[1] if b_mn_major else weight.shape[0]
+        assert x_shard.is_contiguous() and x_shard.dtype == torch.bfloat16
+        assert M <= self.max_rows and K <= self.max_k, (M, K, self.max_rows, self.max_k)
+        self.ag_epoch += 1
+        e = self.ag_epoch
+        stage = e % 2
+        st = L.stream_ptr()
+        gathered = torch.empty(M, K, device=self.device, dtype=torch.bfloat16)
+        own = gathered[self.rank * rpc:(self.rank + 1) * rpc]
+        addrs = (C.c_void_p * 8)()
+        n = 0
+        for r in range(self.tp):
+            if r != self.rank:
+                addrs[n] = self._flag(r, self.w_ready + self.rank)      # rank r's shard_ready[me]
+                n += 1
+        # wait (peers pulled this staging shard's previous content, epoch e-2) + copy + signal
+        L.call("b200_stage_shard", x_shard.data_ptr(), self._stage(self.rank, stage), own.data_ptr(),
+               rpc * K * 2, self._flag(self.rank, self.w_consumed), self.tp, self.rank, (e - 2) & 0xFFFFFFFF,
+               int(e > 2), self._flag(self.rank, self.w_stage_done), e, addrs, n, e, st)
+        out = torch.empty(M, N, device=self.device, dtype=torch.bfloat16)
+        L.call("b200_gemm_allgather", C.byref(self._descs[stage]), gathered.data_ptr(), weight.data_ptr(),
+               out.data_ptr(), M, N, K, int(b_mn_major), weight.stride(0), N, e, st)
+        return out, gathered
+
+    # ---- GEMM -> reduce-scatter ------------------------------------------------------------
+    def gemm_reduce_scatter(self, a: torch.Tensor, weight: torch.Tensor, b_mn_major: bool = False):
+        """a [M, K_local], weight [N, K_local] (or [K_local, N]); returns this rank's rows
+        [M/tp, N] of the sum over ranks."""
+        M, K = a.shape
+        N = weight.shape[1] if b_mn_major else weight.shape[0]
+        rpc = M // self.tp
+        assert a.dtype == torch.bfloat16 and a.stride(1) == 1
+        assert M <= self.max_rows and N <= self.max_n, (M, N, self.max_rows, self.max_n)
+        self.rs_calls += 1
+        s = self.rs_calls % 2
+        arrivals = L.lib().b200_gemm_rs_arrivals(N, self.tp)
+        parts = (C.c_void_p * 8)()
+        for r in range(self.tp):
+            parts[r] = self._parts(r, s)
+        out = torch.empty(rpc, N, device=self.device, dtype=torch.bfloat16)
+        L.call("b200_gemm_reduce_scatter", C.byref(self._descs[0]), parts, s, a.data_ptr(), weight.data_ptr(),
+               out.data_ptr(), M, N, K, int(b_mn_major), a.stride(0), weight.stride(0),
+               arrivals, L.stream_ptr())
+        return out
+
+    def check(self):
+        """Synchronise and raise if a cross-GPU wait timed out since the last check (debug / tests)."""
+        torch.cuda.synchronize()
+        rec = (C.c_uint * 8)()
+        L.call("b200_comm_debug_read", rec, launches=0)
+        if rec[0]:
+            site = {1: "row block not delivered by the copier warps", 2: "peer shard_ready flag",
+                    3: "reduce-scatter arrivals"}.get(rec[0], str(rec[0]))
+            raise RuntimeError(f"fused collective wait timed out: {site}; block {rec[1]}, saw {rec[2]}, "
+                               f"wanted {rec[3]}, epoch {rec[4]}, mode {rec[5]}, rank {rec[6]}, index {rec[7]}")
+
+    def close(self):
+        torch.cuda.synchronize()
+        for r, p in enumerate(self.peer_base):
+            if r != self.rank:
+                L.lib().b200_symm_unmap(C.c_void_p(p))
+        L.lib().b200_symm_free(C.c_void_p(self.base))
+
+
+_WORKSPACE = None
+
+
+def get_workspace(group, max_rows, max_k, max_n):
+    """Process-wide workspace of the tensor-parallel group, grown on demand (collective: all
+    ranks must ask for the same sizes)."""
+    global _WORKSPACE
+    ws = _WORKSPACE
+    if ws is None or ws.max_rows < max_rows or ws.max_k < max_k or ws.max_n < max_n:
+        if ws is not None:
+            max_rows, max_k, max_n = max(max_rows, ws.max_rows), max(max_k, ws.max_k), max(max_n, ws.max_n)
+            dist.barrier(group=group)
+            ws.close()
+        ws = _WORKSPACE = TPWorkspace(group, max_rows, max_k, max_n)
+    return ws

@@ -95,11 +95,15 @@ class _RMSNormFn(torch.autograd.Function):
         main = getattr(w, "main_grad", None)
         fuse = main is not None and main.dtype == torch.float32 and getattr(w, "_b200_fuse_wgrad", False)
         dw = main if fuse else torch.empty(H, device=dy.device, dtype=torch.float32)
+        # the grad buffer is only "logically" zeroed at the start of a step: the first gradient
+        # of the step must overwrite the slice, later ones (more micro-batches) accumulate
+        first = fuse and getattr(w, "_b200_main_grad_empty", False)
         L.call("b200_rmsnorm_bwd", dy2.data_ptr(), xin.data_ptr(), weight.data_ptr(),
                rstd.data_ptr(), L.ptr(dres), dx.data_ptr(), dw.data_ptr(), scratch.data_ptr(), M, H,
-               1 if fuse else 0, L.stream_ptr(), launches=2)
+               1 if (fuse and not first) else 0, L.stream_ptr(), launches=2)
         dxv = dx.view(ctx.shape)
         if fuse:
+            w._b200_main_grad_empty = False
             _notify_grad_ready(w)
             gw = None
         else:

@@ -102,14 +102,28 @@ def _communicate(tensor_send_next, tensor_send_prev, recv_prev, recv_next, tenso
     prev_rank = mpu.get_pipeline_model_parallel_prev_rank()
     next_rank = mpu.get_pipeline_model_parallel_next_rank()
     ops = []
-    if tensor_send_prev is not None:
-        ops.append(dist.P2POp(dist.isend, tensor_send_prev.contiguous(), prev_rank))
-    if tensor_recv_prev is not None:
-        ops.append(dist.P2POp(dist.irecv, tensor_recv_prev, prev_rank))
-    if tensor_send_next is not None:
-        ops.append(dist.P2POp(dist.isend, tensor_send_next.contiguous(), next_rank))
-    if tensor_recv_next is not None:
-        ops.append(dist.P2POp(dist.irecv, tensor_recv_next, next_rank))
+    if prev_rank == next_rank:
+        # Two stages: the neighbour in both directions is the same rank, and sends / receives
+        # between one pair of ranks are matched in posting order. Our "send to prev" (a gradient)
+        # is the peer's "receive from next", so the receives are posted next-first. (The reference
+        # avoids the case by refusing interleaving for pp == 2, megatron/arguments.py:117-120.)
+        if tensor_send_prev is not None:
+            ops.append(dist.P2POp(dist.isend, tensor_send_prev.contiguous(), prev_rank))
+        if tensor_send_next is not None:
+            ops.append(dist.P2POp(dist.isend, tensor_send_next.contiguous(), next_rank))
+        if tensor_recv_next is not None:
+            ops.append(dist.P2POp(dist.irecv, tensor_recv_next, next_rank))
+        if tensor_recv_prev is not None:
+            ops.append(dist.P2POp(dist.irecv, tensor_recv_prev, prev_rank))
+    else:
+        if tensor_send_prev is not None:
+            ops.append(dist.P2POp(dist.isend, tensor_send_prev.contiguous(), prev_rank))
+        if tensor_recv_prev is not None:
+            ops.append(dist.P2POp(dist.irecv, tensor_recv_prev, prev_rank))
+        if tensor_send_next is not None:
+            ops.append(dist.P2POp(dist.isend, tensor_send_next.contiguous(), next_rank))
+        if tensor_recv_next is not None:
+            ops.append(dist.P2POp(dist.irecv, tensor_recv_next, next_rank))
     if ops:
         if dist.get_backend() == "gloo" and mpu.get_pipeline_model_parallel_world_size() == 2 \
                 and len(ops) > 1:

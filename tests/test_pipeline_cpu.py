@@ -1,0 +1,34 @@
+"""Pipeline and tensor parallel schedules on CPU / Gloo (world size 2): 1F1B, interleaved 1F1B with
+two stages (the 4-way exchange talks to ONE peer in both directions, so the posting order of the
+sends and receives decides which tensor lands where) and TP + sequence parallelism must all follow
+the single-process loss curve of the same tiny Llama."""
+import pytest
+
+from tests.helpers.launch import run_tiny
+
+KW = dict(steps=3, layers=4, num_microbatches=4, backend="gloo", dtype="fp32", hidden=128, heads=4, kv_heads=2,
+          seq=64)
+ENV = {"B200_DISABLE_KERNELS": "1", "CUDA_VISIBLE_DEVICES": ""}
+
+
+@pytest.fixture(scope="module")
+def base():
+    return run_tiny(env_extra=ENV, **KW)["losses"]
+
+
+def _close(a, b, rel):
+    assert len(a) == len(b) > 0
+    for x, y in zip(a, b):
+        assert abs(x - y) <= rel * abs(y), (a, b)
+
+
+def test_pp2_1f1b(base):
+    _close(run_tiny(nproc=2, pp=2, env_extra=ENV, **KW)["losses"], base, 2e-3)
+
+
+def test_pp2_interleaved(base):
+    _close(run_tiny(nproc=2, pp=2, vpp_layers=1, env_extra=ENV, **KW)["losses"], base, 2e-3)
+
+
+def test_tp2_sequence_parallel(base):
+    _close(run_tiny(nproc=2, tp=2, env_extra=ENV, **KW)["losses"], base, 2e-3)

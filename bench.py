@@ -180,6 +180,26 @@ def run_ours(a):
     ms = e0.elapsed_time(e1)
     launches = klib.launch_count() - launches0
 
+    if a.torch_profile:
+        # one step under the torch profiler: per-kernel device time and the GPU-busy fraction
+        from torch.profiler import ProfilerActivity, profile
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            step()
+            torch.cuda.synchronize()
+        if rank == 0:
+            ev = [e for e in prof.key_averages() if e.device_time_total > 0]
+            ev.sort(key=lambda e: -e.device_time_total)
+            tot = sum(e.device_time_total for e in ev)
+            os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+            with open(os.path.join(ROOT, "gpurun_out", f"torch_profile_n{a.gpus}.md"), "w") as f:
+                f.write(f"# one training step, {a.model}, {a.gpus} GPU(s): device time by kernel\n\n")
+                f.write(f"step wall (device-timed, outside the profiler): {ms / a.steps:.1f} ms; "
+                        f"sum of kernel time under the profiler: {tot / 1e3:.1f} ms\n\n")
+                f.write("| share | total ms | calls | avg us | kernel |\n|---|---|---|---|---|\n")
+                for e in ev[:60]:
+                    f.write(f"| {e.device_time_total / tot * 100:.2f}% | {e.device_time_total / 1e3:.2f} | {e.count} | "
+                            f"{e.device_time_total / max(e.count, 1):.1f} | `{e.key[:110]}` |\n")
     # ---- region B: end to end (pinned H2D inputs + D2H loss every step), wall clock ----
     if a.profile:
         sampler.stop()
@@ -287,6 +307,7 @@ def main():
     p.add_argument("--debug_layers", type=int, default=0, help="debug only: override the layer count")
     p.add_argument("--kernels", default="auto", help="debug only: auto|off")
     p.add_argument("--fused_comm", default="auto", help="A/B only: auto|on|off (in-kernel TP collectives)")
+    p.add_argument("--torch_profile", action="store_true", help="also write gpurun_out/torch_profile_nN.md")
     p.add_argument("--profile", action="store_true", help="1 warm-up + K steps, no e2e region; for ncu, NOT a bench value")
     a = p.parse_args()
     if a.warmup < 3 and not a.profile:

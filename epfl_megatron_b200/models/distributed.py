@@ -9,10 +9,11 @@ Differences that matter on B200:
   buffer every step, training.py:397-399);
 * weight gradients of the linear layers are accumulated into ``main_grad`` by the GEMM
   epilogue itself (ops.functional.wgrad_accumulate);
-* the buffer is split into buckets; when ``overlap_grad_reduce`` is on, a bucket's
-  all-reduce / reduce-scatter is launched on the communication stream as soon as the
-  last gradient of the bucket has been produced in the final micro-batch's backward
-  (the reference reduces once, after backward, with no overlap).
+* the buffer is split into buckets in the order gradients are produced; with
+  ``overlap_grad_reduce`` a bucket's data-parallel average is launched (asynchronously, on
+  NCCL's stream) the moment every parameter of the bucket has received its last
+  gradient of the step, i.e. under the rest of the backward pass. The reference reduces
+  once, after backward, with nothing to hide it behind (distributed.py:202-232).
 """
 from __future__ import annotations
 
@@ -69,10 +70,23 @@ class DistributedDataParallelBase(MegatronModule, ABC):
         self.module.load_state_dict(state_dict, strict=strict)
 
 
+class _Bucket:
+    __slots__ = ("dtype", "start", "end", "params", "pending", "early_ok", "launched")
+
+    def __init__(self, dtype, start):
+        self.dtype, self.start, self.end = dtype, start, start
+        self.params, self.pending, self.early_ok, self.launched = [], 0, True, False
+
+
 class DistributedDataParallel(DistributedDataParallelBase):
     def __init__(self, module, accumulate_allreduce_grads_in_fp32, use_contiguous_buffers,
-                 fuse_wgrad: bool = True, group_key_fn=None):
+                 fuse_wgrad: bool = True, group_key_fn=None, overlap_grad_reduce: bool = False,
+                 bucket_mb: float = 256.0):
         super().__init__(module)
+        self.overlap_grad_reduce = overlap_grad_reduce
+        self.bucket_bytes = int(bucket_mb * (1 << 20))
+        self._buckets, self._bucket_of, self._arrivals, self._expected = [], {}, {}, 0
+        self._handles = []
         self.accumulate_allreduce_grads_in_fp32 = accumulate_allreduce_grads_in_fp32
         self.use_contiguous_buffers = use_contiguous_buffers
         if accumulate_allreduce_grads_in_fp32:
@@ -129,6 +143,7 @@ class DistributedDataParallel(DistributedDataParallelBase):
                 p._b200_fuse_wgrad = bool(fuse_wgrad and dt == torch.float)
                 p._b200_main_grad_empty = False
                 self._grad_buffer_param_index_map.setdefault(dt, {})[p] = (start, end)
+        self._build_buckets()
         self.grad_accs = []
         for p in self._params:
             tmp = p.expand_as(p)
@@ -150,11 +165,82 @@ class DistributedDataParallel(DistributedDataParallelBase):
                     cb()
         return hook
 
+    # ---- bucketed, overlapped data-parallel reduction ----------------------------------------
+    def _build_buckets(self):
+        """Contiguous index ranges of each grad buffer, cut at parameter boundaries once a range
+        holds ``bucket_bytes``. Buffer order == order in which backward produces the gradients."""
+        for dt, items in self.layout.items():
+            esz = self._grad_buffers[dt].data.element_size()
+            cur = None
+            for p, start, end, _ in items:
+                if cur is None:
+                    cur = _Bucket(dt, start)
+                    self._buckets.append(cur)
+                cur.params.append(p)
+                cur.end = end
+                if getattr(p, "shared", False):
+                    cur.early_ok = False       # tied weights receive several gradients per micro-batch
+                self._bucket_of[p] = cur
+                if (cur.end - cur.start) * esz >= self.bucket_bytes:
+                    cur = None
+            if cur is not None or items:
+                # the padding at the end of the buffer travels with the last bucket
+                self._buckets[-1].end = self._grad_buffers[dt].numel_padded
+        for p in self._params:
+            p._b200_grad_ready = (lambda q=p: self._on_grad_ready(q))
+
+    def _on_grad_ready(self, p):
+        """Called (stream-ordered) after a gradient contribution of ``p`` was written."""
+        if not self._expected:
+            return
+        n = self._arrivals.get(p, 0) + 1
+        self._arrivals[p] = n
+        if n != self._expected:
+            return
+        b = self._bucket_of[p]
+        b.pending -= 1
+        if b.pending == 0 and b.early_ok and not b.launched:
+            self._launch(b, async_op=True)
+
+    def _launch(self, b, async_op):
+        b.launched = True
+        view = self._grad_buffers[b.dtype].data[b.start:b.end]
+        grp = mpu.get_data_parallel_group()
+        avg = dist.ReduceOp.AVG if view.is_cuda else dist.ReduceOp.SUM
+        if not view.is_cuda:
+            view.mul_(1.0 / mpu.get_data_parallel_world_size())
+        h = dist.all_reduce(view, op=avg, group=grp, async_op=async_op)
+        if async_op:
+            self._handles.append(h)
+
+    def finish_grad_reduce(self) -> bool:
+        """Reduce whatever was not launched during backward and wait for everything. Returns True
+        when this wrapper averaged its whole buffer over the data-parallel group (the optimizer
+        then skips its own reduction), False when overlap is off."""
+        if not self._expected:
+            return False
+        for b in self._buckets:
+            if not b.launched:
+                self._launch(b, async_op=False)
+        for h in self._handles:
+            h.wait()
+        self._handles = []
+        self._expected = 0
+        return True
+
     def zero_grad_buffer(self):
         """Logical zero: the next gradient written to each slice overwrites it."""
         assert self._grad_buffers is not None, "buffers are not initialized."
         for p in self._params:
             p._b200_main_grad_empty = True
+        self._expected = 0
+        if self.overlap_grad_reduce and self._buckets and mpu.get_data_parallel_world_size() > 1 \
+                and dist.is_initialized():
+            from .. import global_vars
+            self._expected = global_vars.get_num_microbatches()
+            self._arrivals = {}
+            for b in self._buckets:
+                b.pending, b.launched = len(b.params), False
 
     def finalize_grad_buffer(self):
         """Physically zero the slices that received no gradient this step."""

@@ -252,6 +252,8 @@ class FlatOptimizer(MegatronOptimizer):
         if dp > 1:
             grp = mpu.get_data_parallel_group()
             for ch in self.chunks:
+                if ch.ddp.finish_grad_reduce():
+                    continue     # averaged bucket by bucket under the backward pass
                 if self._use_kernels:
                     L.call("b200_scale", ch.grad.data_ptr(), ch.N, None, 1.0 / dp, L.stream_ptr())
                 else:

@@ -176,7 +176,9 @@ def get_model(model_provider_func, model_type=ModelType.encoder_or_decoder, wrap
                                        getattr(args, "_lr_mult", 1.0))
             model = [LocalDDP(m, args.accumulate_allreduce_grads_in_fp32,
                               args.use_contiguous_buffers_in_local_ddp,
-                              fuse_wgrad=args.gradient_accumulation_fusion, group_key_fn=key_fn) for m in model]
+                              fuse_wgrad=args.gradient_accumulation_fusion, group_key_fn=key_fn,
+                              overlap_grad_reduce=getattr(args, "overlap_grad_reduce", True),
+                              bucket_mb=getattr(args, "ddp_bucket_mb", 256)) for m in model]
             if args.data_parallel_random_init:
                 for m in model:
                     m.broadcast_params()

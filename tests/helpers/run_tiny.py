@@ -32,6 +32,9 @@ def main():
     p.add_argument("--save", default=None)
     p.add_argument("--load", default=None)
     p.add_argument("--num_microbatches", type=int, default=2)
+    p.add_argument("--no_overlap", action="store_true")
+    p.add_argument("--bucket_mb", type=int, default=None)
+    p.add_argument("--fused_comm", default="auto")
     a = p.parse_args()
 
     import torch
@@ -68,6 +71,11 @@ def main():
         argv.append("--sequence_parallel")
     if a.dist_opt:
         argv.append("--use_distributed_optimizer")
+    if a.no_overlap:
+        argv.append("--no_overlap_grad_reduce")
+    if a.bucket_mb is not None:
+        argv += ["--ddp_bucket_mb", str(a.bucket_mb)]
+    argv += ["--b200_fused_comm", a.fused_comm]
     if a.recompute:
         argv += ["--recompute_granularity", "full", "--recompute_method", "uniform"]
     if a.vpp_layers:

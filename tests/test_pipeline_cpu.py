@@ -32,3 +32,13 @@ def test_pp2_interleaved(base):
 
 def test_tp2_sequence_parallel(base):
     _close(run_tiny(nproc=2, tp=2, env_extra=ENV, **KW)["losses"], base, 2e-3)
+
+
+def test_dp2_overlapped_bucketed_grad_reduce_matches_single_reduce():
+    """Gradients averaged bucket by bucket during backward (many small buckets) == one reduction
+    after backward, for the plain and the distributed optimizer."""
+    kw = dict(KW, num_microbatches=2, layers=2)
+    ref = run_tiny(nproc=2, no_overlap=True, env_extra=ENV, **kw)["losses"]
+    for extra in (dict(bucket_mb=0), dict(bucket_mb=0, dist_opt=True)):
+        got = run_tiny(nproc=2, env_extra=ENV, **kw, **extra)["losses"]
+        _close(got, ref, 1e-5)

@@ -73,6 +73,12 @@ __device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t* r)
 __device__ __forceinline__ void tmem_st_wait_b() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
+// 2^x: one MUFU.EX2 (masked-out entries may overflow to +inf here; they are replaced by 0 below)
+__device__ __forceinline__ float bwd_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 // D[tmem] (+)= A[tmem] * B[smem]: the A operand (bf16 pairs, one row per TMEM lane) is read
 // from tensor memory.
 __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b,
@@ -408,7 +414,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int t = 0; t < 32; ++t) {
           const int c = half * 64 + ch * 32 + t;
           const float l2 = kIsKV ? vec[c] : my_lse2;
-          float p = exp2f(__uint_as_float(sr[t]) * scale_log2 - l2);
+          float p = bwd_ex2(fmaf(__uint_as_float(sr[t]), scale_log2, -l2));
           if (need_mask) {
             const int ycol = ycol0 + ch * 32 + t;
             bool vis;

@@ -286,6 +286,13 @@ __global__ void colsum2_kernel(const float* __restrict__ partial, float* __restr
   if (dbeta) dbeta[c] = accumulate ? dbeta[c] + t : t;
 }
 
+bool rmsnorm_warp_ok(int H);
+void rmsnorm_fwd_warp(const void* x, const void* residual, const void* w, void* y, void* h_out,
+                      float* rstd, int M, int H, float eps, cudaStream_t stream);
+void rmsnorm_bwd_warp(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                      void* dx, float* dw, float* scratch, int max_strips, int M, int H, int accumulate,
+                      cudaStream_t stream);
+
 static inline bool norm_shape_ok(int M, int H) {
   return M > 0 && H > 0 && (H % 8) == 0 && H <= kNormThreads * kNormMaxVec * 8;
 }
@@ -301,6 +308,11 @@ B200_API int b200_rmsnorm_fwd(const void* x, const void* residual, const void* w
                               void* h_out, float* rstd, int M, int H, float eps,
                               cudaStream_t stream) {
   if (!norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
+  if (rmsnorm_warp_ok(H)) {   // one warp per row (csrc/norm_warp.cu)
+    rmsnorm_fwd_warp(x, residual, w, y, h_out, rstd, M, H, eps, stream);
+    B200_CHECK_LAUNCH();
+    return 0;
+  }
   int grid = M < 8 * kNumSMs ? M : 8 * kNumSMs;
   if (residual)
     rmsnorm_fwd_kernel<true><<<grid, kNormThreads, 0, stream>>>(
@@ -320,6 +332,11 @@ B200_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, cons
                               int accumulate, cudaStream_t stream) {
   if (!norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
   int grid = b200_norm_bwd_grid(M);
+  if (rmsnorm_warp_ok(H)) {
+    rmsnorm_bwd_warp(dy, x, w, rstd, dres, dx, dw, scratch, grid, M, H, accumulate, stream);
+    B200_CHECK_LAUNCH();
+    return 0;
+  }
   if (dres)
     rmsnorm_bwd_kernel<true><<<grid, kNormThreads, 0, stream>>>(
         (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, rstd,

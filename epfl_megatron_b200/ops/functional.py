@@ -394,7 +394,7 @@ class _AttnFusedQKVFn(torch.autograd.Function):
         lse = torch.empty(b, np_, s, device=qkv.device, dtype=torch.float32)
         ss, sb, sg, sj = qkv.stride(0), qkv.stride(1), qkv.stride(2), qkv.stride(3)
         base = qkv.data_ptr()
-        L.call("b200_attn_fwd", base, base + qpg * sj * 2, base + (qpg + 1) * sj * 2,
+        L.call(_ATTN_FWD_ENTRY, base, base + qpg * sj * 2, base + (qpg + 1) * sj * 2,
                out.data_ptr(), lse.data_ptr(), s, s, b, g, qpg, hn, ss, sb, sg, sj, ss, sb, sg,
                float(scale), int(causal), L.stream_ptr())
         ctx.save_for_backward(qkv, out, lse)
@@ -435,6 +435,7 @@ class _AttnFusedQKVFn(torch.autograd.Function):
 
 
 _ATTN_BWD = "own"   # own | fa2
+_ATTN_FWD_ENTRY = "b200_attn_fwd_v2"   # two query tiles per CTA; "b200_attn_fwd" = first generation
 
 
 def set_attn_bwd_mode(mode: str):

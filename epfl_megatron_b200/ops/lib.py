@@ -47,6 +47,8 @@ _SIGNATURES = {
     "b200_gemm_bf16_variant": ([vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, i32, i32, vp], i32),
     "b200_attn_fwd": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
                        i64, i64, f32, i32, vp], i32),
+    "b200_attn_fwd_v2": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i64, i64, i64, i64, i64,
+                          i64, i64, f32, i32, vp], i32),
     "b200_attn_bwd_scratch_elems": ([i32, i32, i32, i32, i32], i64),
     "b200_attn_bwd": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
                        i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64,

@@ -65,6 +65,14 @@ def check_rmsnorm(M=1024, H=4096):
                launches=2)
         out[f"dx_res{int(use_res)}"] = _close(dx, hf.grad, 2e-2, 2e-2, "rmsnorm dx")
         out[f"dw_res{int(use_res)}"] = _close(dw, wf.grad, 0.5, 2e-2, "rmsnorm dw")
+        # gradient arriving through the residual branch + accumulation into dw
+        dres = torch.randn(M, H, device=dev).bfloat16()
+        dx2 = torch.empty_like(x)
+        L.call("b200_rmsnorm_bwd", dy.data_ptr(), hin.data_ptr(), w.data_ptr(), rstd.data_ptr(),
+               dres.data_ptr(), dx2.data_ptr(), dw.data_ptr(), scratch.data_ptr(), M, H, 1, L.stream_ptr(),
+               launches=2)
+        _close(dx2, hf.grad + dres.float(), 3e-2, 2e-2, "rmsnorm dx + dres")
+        _close(dw, 2 * wf.grad, 1.0, 2e-2, "rmsnorm dw accumulate")
     return out
 
 
@@ -371,7 +379,10 @@ def attn_ref(q, k, v, scale, causal):
     return o.permute(2, 0, 1, 3).contiguous(), lse
 
 
-def attn_fwd_fused_qkv(qkv, G, qpg, hn, scale, causal=True):
+ATTN_FWD_ENTRY = "b200_attn_fwd_v2"    # two-tile ping-pong kernel; "b200_attn_fwd" = first generation
+
+
+def attn_fwd_fused_qkv(qkv, G, qpg, hn, scale, causal=True, entry=None):
     """qkv: [s, b, G, qpg+2, hn] bf16 (the fused projection output). Returns out, lse."""
     s, b = qkv.shape[0], qkv.shape[1]
     np_ = G * qpg
@@ -380,18 +391,18 @@ def attn_fwd_fused_qkv(qkv, G, qpg, hn, scale, causal=True):
     ss, sb, sg, sj = qkv.stride(0), qkv.stride(1), qkv.stride(2), qkv.stride(3)
     base = qkv.data_ptr()
     esz = 2
-    L.call("b200_attn_fwd", base, base + qpg * sj * esz, base + (qpg + 1) * sj * esz,
+    L.call(entry or ATTN_FWD_ENTRY, base, base + qpg * sj * esz, base + (qpg + 1) * sj * esz,
            out.data_ptr(), lse.data_ptr(), s, s, b, G, qpg, hn, ss, sb, sg, sj, ss, sb, sg,
            float(scale), int(causal), L.stream_ptr())
     return out, lse
 
 
-def check_attn_fwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True):
+def check_attn_fwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True, entry=None):
     dev = _dev()
     torch.manual_seed(10)
     qkv = torch.randn(S, B, G, QPG + 2, HN, device=dev).bfloat16()
     scale = 1.0 / math.sqrt(HN)
-    out, lse = attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, causal)
+    out, lse = attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, causal, entry=entry)
     q = qkv[:, :, :, :QPG].reshape(S, B, G * QPG, HN)
     k = qkv[:, :, :, QPG]
     v = qkv[:, :, :, QPG + 1]
@@ -424,6 +435,10 @@ def check_attn_bwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True):
 
 CHECKS = {
     "rmsnorm": check_rmsnorm,
+    "rmsnorm_h1024": lambda: check_rmsnorm(777, 1024),
+    "rmsnorm_h5120": lambda: check_rmsnorm(300, 5120),
+    "rmsnorm_h8192_cta_path": lambda: check_rmsnorm(256, 8192),
+    "rmsnorm_h1000_cta_path": lambda: check_rmsnorm(128, 1000),
     "layernorm": check_layernorm,
     "rope": check_rope,
     "glu": check_glu,
@@ -456,6 +471,11 @@ CHECKS = {
     "attn_fwd": check_attn_fwd,
     "attn_fwd_mqa_long": lambda: check_attn_fwd(1024, 1, 1, 8, 128, True),
     "attn_fwd_full": lambda: check_attn_fwd(384, 1, 2, 2, 128, False),
+    "attn_fwd_ragged": lambda: check_attn_fwd(328, 1, 1, 2, 128, True),
+    "attn_fwd_one_tile": lambda: check_attn_fwd(128, 1, 1, 1, 128, True),
+    "attn_fwd_long": lambda: check_attn_fwd(2048, 1, 2, 1, 128, True),
+    "attn_fwd_gen1": lambda: check_attn_fwd(entry="b200_attn_fwd"),
+    "attn_fwd_gen1_mqa_long": lambda: check_attn_fwd(1024, 1, 1, 8, 128, True, entry="b200_attn_fwd"),
     "attn_bwd_small": lambda: check_attn_bwd(128, 1, 1, 1, 128, True),
     "attn_bwd_mha": lambda: check_attn_bwd(512, 2, 4, 1, 128, True),
     "attn_bwd_gqa": check_attn_bwd,

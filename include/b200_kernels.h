@@ -138,6 +138,13 @@ int b200_attn_fwd(const void* q, const void* k, const void* v, void* out, float*
                   long long q_sj, long long k_ss, long long k_sb, long long k_sg,
                   float softmax_scale, int causal, cudaStream_t stream);
 
+/* Second-generation forward (csrc/attn_fwd_v2_tcgen05.cu): two 128-row query tiles per CTA ping-pong
+ * through the tensor core, P stays in TMEM, KV blocks of 128. Same arguments and reference call site. */
+int b200_attn_fwd_v2(const void* q, const void* k, const void* v, void* out, float* lse, int sq, int sk,
+                     int B, int G, int qpg, int hn, long long q_ss, long long q_sb, long long q_sg,
+                     long long q_sj, long long k_ss, long long k_sb, long long k_sg,
+                     float softmax_scale, int causal, cudaStream_t stream);
+
 /* Attention backward (csrc/attn_bwd_tcgen05.cu): dq/dk/dv written with their own element strides,
  * e.g. straight into the gradient of the fused QKV tensor; the GQA reduction of dk/dv over the
  * query heads of a group happens in TMEM (plus fp32 partial sums in scratch when few KV heads would

@@ -1,0 +1,5 @@
+set -x
+timeout 600 python -m epfl_megatron_b200.ops.selfcheck attn_bwd_small attn_bwd_mha attn_bwd_gqa attn_bwd_mqa_long attn_bwd_full attn_bwd_ragged > gpurun_out/selfcheck_attn_bwd.log 2>&1; echo "selfcheck rc=$?"; grep -v SUMMARY gpurun_out/selfcheck_attn_bwd.log | cut -c1-300
+timeout 300 python tools/kernel_bench.py attn_bwd > gpurun_out/kb_attn_bwd2.log 2>&1; cat gpurun_out/kb_attn_bwd2.log | cut -c1-330
+timeout 900 python -m pytest tests -m "gpu and not multigpu" -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench_ours.log 2>&1; echo "bench rc=$?"; tail -1 gpurun_out/bench_ours.log | cut -c1-330

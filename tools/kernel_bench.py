@@ -110,8 +110,9 @@ def bench_attn():
         scale = 1 / math.sqrt(HN)
         fl = 4.0 * S * S * G * QPG * HN * B / 2
         t_own = timeit(lambda: SC.attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, True))
+        t_gen1 = timeit(lambda: SC.attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, True, entry="b200_attn_fwd"))
         rec = dict(kernel="attn_fwd", shape=name, S=S, heads=G * QPG, kv_heads=G, ms_own=t_own,
-                   tflops_own=fl / t_own / 1e9)
+                   tflops_own=fl / t_own / 1e9, ms_own_gen1=t_gen1, tflops_own_gen1=fl / t_gen1 / 1e9)
         if flash_attn_func is not None:
             def ref_path():
                 # what the reference does: expand K/V to all heads, [s,b]->[b,s] copies

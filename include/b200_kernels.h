@@ -127,6 +127,34 @@ int b200_gemm_bf16_variant(const void* A, const void* B, void* C, int M, int N, 
                            long long ldc, int out_mode, int max_ctas, int variant,
                            cudaStream_t stream);
 
+/* ---- peer memory + fused tensor-parallel GEMMs (csrc/comm.cu, csrc/gemm_comm_tcgen05.cu) ----
+ * The reference moves every tensor-parallel activation through NCCL calls around cuBLAS GEMMs
+ * (megatron/core/tensor_parallel/layers.py:225-243, :691-692; mappings.py:89-124); here the gather /
+ * scatter happens inside the GEMM kernel over CUDA-IPC mapped peer memory. */
+int b200_symm_alloc(long long bytes, void** out);            /* cudaMalloc + zero */
+int b200_symm_free(void* p);
+int b200_symm_export(void* p, void* handle64);               /* cudaIpcMemHandle_t, 64 bytes */
+int b200_symm_import(const void* handle64, void** out);      /* map a peer's region */
+int b200_symm_unmap(void* p);
+int b200_symm_signal(unsigned* const* addrs, int n, unsigned value, cudaStream_t stream);
+int b200_symm_wait(const unsigned* flags, int n, int skip, unsigned value, cudaStream_t stream);
+int b200_copy2(const void* src, void* dst0, void* dst1, long long bytes, cudaStream_t stream);
+int b200_stage_shard(const void* src, void* stage, void* own_rows, long long bytes, const unsigned* consumed,
+                     int tp, int rank, unsigned wait_value, int do_wait, unsigned* done_counter,
+                     unsigned call_index, unsigned* const* signal_addrs, int n_signal, unsigned epoch,
+                     cudaStream_t stream);
+int b200_comm_flag_words(int max_blocks);
+int b200_comm_shard_ready_word(int max_blocks);
+int b200_comm_consumed_word(int max_blocks);
+int b200_comm_debug_read(unsigned* out8);
+typedef struct { int tp, rank; void* peer_stage[8]; unsigned* peer_flags[8]; int max_blocks; } B200CommDesc;
+int b200_gemm_allgather(const B200CommDesc* d, void* gathered, const void* B, void* C, int M, int N, int K,
+                        int b_mn_major, long long ldb, long long ldc, unsigned epoch, cudaStream_t stream);
+int b200_gemm_rs_arrivals(int N, int tp);
+int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int set, const void* A,
+                             const void* B, void* out, int M, int N, int K, int b_mn_major, long long lda,
+                             long long ldb, unsigned rs_target, cudaStream_t stream);
+
 /* ---- tcgen05 attention (csrc/attn_fwd_tcgen05.cu) --------------------------------------- */
 /* Causal / full GQA attention forward reading q, k, v through arbitrary element strides
  * (the fused QKV projection layout [s, b, g, q_per_g+2, hn] needs no copies). hn must be 128.

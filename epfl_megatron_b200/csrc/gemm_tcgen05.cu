@@ -259,7 +259,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 // multicast tcgen05.commit; tmem_empty[as] lives in the leader and is arrived on by one
 // lane of each of the 8 epilogue warps of the pair (remote arrive for the peer).
 // ---------------------------------------------------------------------------------
-constexpr int kPairStages = 6;
+constexpr int kPairStages = 5;
 constexpr int kPairBN = 256;       // instruction N; each CTA stages kPairBN / 2 rows of B
 constexpr int kPairHalfN = kPairBN / 2;
 
@@ -267,14 +267,24 @@ struct PairSmem {
   static constexpr int kABytes = kBM * kBK * 2;          // 16 KB
   static constexpr int kBBytes = kPairHalfN * kBK * 2;   // 16 KB
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kBarOffset = kPairStages * kStageBytes;
+  static constexpr int kOutBox = kBM * 128;              // [128 rows x 128 B]: 64 bf16 or 32 fp32 columns
+  static constexpr int kOutOffset = kPairStages * kStageBytes;
+  static constexpr int kBarOffset = kOutOffset + 2 * kOutBox;
   static constexpr int kTotal = kBarOffset + 256 + 1024;
 };
+
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+      ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+      : "memory");
+}
 
 template <bool kAMN, bool kBMN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                      void* __restrict__ Cout, int M, int N, int K, long long ldc, int out_mode) {
+                      const __grid_constant__ CUtensorMap tmC, void* __restrict__ Cout, int M, int N, int K,
+                      long long ldc, int out_mode, int tma_epilogue) {
   using L = PairSmem;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -390,33 +400,106 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
   } else if (warp >= 4) {
     // ------------------------------ epilogue (both CTAs) ----------------------
+    // TMEM -> registers -> 128-byte-swizzled shared-memory box -> TMA: a plain tile store (bf16 / fp32)
+    // or, for out_mode 2, cp.reduce.async.bulk .add.f32 so the `main_grad += dY^T X` accumulation
+    // happens in L2 with full-line writes instead of a read-modify-write through the SM. Two boxes
+    // alternate. C that TMA cannot address (odd strides / alignment) takes the direct-store path.
     const int ew = warp - 4;
+    const int r = ew * 32 + lane;
     int as = 0;
     uint32_t aphase = 0;
     const uint32_t leader_empty0 = mapa_u32(smem_u32(&tmem_empty[0]), 0);
+    uint8_t* stage_out = smem + L::kOutOffset;
+    const bool issuer = (ew == 0 && lane == 0);
+    uint32_t box_count = 0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int tm, tn;
       tile_coords(tile, tiles_m, tiles_n, tm, tn);
-      const int row = tm * 2 * kBM + static_cast<int>(rank) * kBM + ew * 32 + lane;
+      const int row0 = tm * 2 * kBM + static_cast<int>(rank) * kBM;
+      const int row = row0 + r;
       const int n0 = tn * kPairBN;
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kPairBN;
+      if (!tma_epilogue) {
 #pragma unroll 1
-      for (int c = 0; c < kPairBN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c * 32, r);
-        tmem_ld_wait();
-        store_acc_chunk(r, Cout, row, n0 + c * 32, M, N, ldc, out_mode);
+        for (int c = 0; c < kPairBN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+          store_acc_chunk(v, Cout, row, n0 + c * 32, M, N, ldc, out_mode);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(leader_empty0 + as * 8);
+      } else if (out_mode == 0) {
+#pragma unroll 1
+        for (int bx = 0; bx < kPairBN / 64; ++bx) {
+          uint8_t* box = stage_out + (box_count & 1) * L::kOutBox;
+          if (issuer) tma_store_wait_read<1>();      // the store two boxes ago has drained this buffer
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v[32];
+            tmem_ld_32x32(taddr + (2 * bx + h) * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 o;
+              o.x = pack_bf16x2(__uint_as_float(v[8 * q + 0]), __uint_as_float(v[8 * q + 1]));
+              o.y = pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3]));
+              o.z = pack_bf16x2(__uint_as_float(v[8 * q + 4]), __uint_as_float(v[8 * q + 5]));
+              o.w = pack_bf16x2(__uint_as_float(v[8 * q + 6]), __uint_as_float(v[8 * q + 7]));
+              *reinterpret_cast<uint4*>(box + sw128_offset(r, h * 4 + q)) = o;
+            }
+          }
+          if (bx == kPairBN / 64 - 1) {          // every accumulator column of this tile has been read
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(leader_empty0 + as * 8);
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (issuer && row0 < M && n0 + bx * 64 < N) {
+            tma_store_2d(&tmC, box, n0 + bx * 64, row0);
+            tma_store_commit();
+          }
+          ++box_count;
+        }
+      } else {
+#pragma unroll 1
+        for (int bx = 0; bx < kPairBN / 32; ++bx) {
+          uint8_t* box = stage_out + (box_count & 1) * L::kOutBox;
+          if (issuer) tma_store_wait_read<1>();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          uint32_t v[32];
+          tmem_ld_32x32(taddr + bx * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            *reinterpret_cast<uint4*>(box + sw128_offset(r, q)) =
+                make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          if (bx == kPairBN / 32 - 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(leader_empty0 + as * 8);
+          }
+          fence_proxy_async_smem();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (issuer && row0 < M && n0 + bx * 32 < N) {
+            if (out_mode == 2) tma_reduce_add_2d(&tmC, box, n0 + bx * 32, row0);
+            else tma_store_2d(&tmC, box, n0 + bx * 32, row0);
+            tma_store_commit();
+          }
+          ++box_count;
+        }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(leader_empty0 + as * 8);
       if (++as == 2) {
         as = 0;
         aphase ^= 1;
       }
     }
+    if (issuer) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -482,6 +565,22 @@ int make_tmap_2d(CUtensorMap* map, const void* base, long long rows, long long c
   return r == CUDA_SUCCESS ? 0 : B200_ERR_BAD_ARG;
 }
 
+// Output map for the TMA epilogue: [rows, cols] of bf16 (box 64 cols) or fp32 (box 32 cols), 128 rows
+// per box, 128-byte swizzle. Returns B200_ERR_UNSUPPORTED when TMA cannot address this C.
+int make_tmap_out(CUtensorMap* map, void* base, long long rows, long long cols, long long ld, bool fp32) {
+  EncodeTiledFn fn = get_encode_fn();
+  const int esz = fp32 ? 4 : 2;
+  if (!fn || (reinterpret_cast<uintptr_t>(base) & 15) || (ld * esz) % 16) return B200_ERR_UNSUPPORTED;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)kBM};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base,
+                  dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : B200_ERR_UNSUPPORTED;
+}
+
 template <int BN, bool kAMN, bool kBMN>
 int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, int K,
                 long long ldc, int out_mode, int max_ctas, cudaStream_t stream) {
@@ -515,7 +614,11 @@ int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int 
   const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + kPairBN - 1) / kPairBN);
   int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
   if (max_ctas > 1 && pairs > max_ctas / 2) pairs = max_ctas / 2;
-  kern<<<2 * pairs, kGemmThreads, PairSmem::kTotal, stream>>>(ta, tb, C, M, N, K, ldc, out_mode);
+  CUtensorMap tc;
+  const int tma_epilogue = make_tmap_out(&tc, C, M, N, ldc, out_mode != 0) == 0 ? 1 : 0;
+  if (!tma_epilogue) tc = ta;   // unused; any valid map
+  kern<<<2 * pairs, kGemmThreads, PairSmem::kTotal, stream>>>(ta, tb, tc, C, M, N, K, ldc, out_mode,
+                                                              tma_epilogue);
   B200_CHECK_LAUNCH();
   return 0;
 }

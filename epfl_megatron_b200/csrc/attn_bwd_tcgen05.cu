@@ -35,14 +35,23 @@ constexpr int kBwdThreads = 384;  // warp0 TMA, warp1 MMA, warp2 TMEM alloc, war
 constexpr int kTileBytes = kBwdT * kBwdT * 2;  // 32 KB: two [128 x 128 B] swizzled boxes
 constexpr int kBoxBytes = kBwdT * 128;         // 16 KB
 
+// Shared memory (exactly 1024-aligned, no slack: the dynamic segment starts at the base of the
+// CTA's window because the kernel has no static shared memory; checked at run time):
+//   Xa, Xb            stationary tiles                      2 x 32 KB
+//   Ya ring (3)       streamed tile used FIRST and LAST in an iteration (K_j / Q_i): needs the
+//                     extra stage so its reload is issued a full iteration before it is needed
+//   Yb ring (2)       streamed tile used only early in the iteration (V_j / dO_i)
+//   vec (2)           LSE*log2e and D of the streamed query block (KV pass)
 struct BwdSmem {
   static constexpr int kXa = 0;
   static constexpr int kXb = kXa + kTileBytes;
-  static constexpr int kY = kXb + kTileBytes;          // stage s: Ya at kY + s*64K, Yb + 32K
-  static constexpr int kVec = kY + 4 * kTileBytes;     // stage s: lse2[128], D[128] fp32
+  static constexpr int kYa = kXb + kTileBytes;          // 3 stages
+  static constexpr int kYb = kYa + 3 * kTileBytes;      // 2 stages
+  static constexpr int kVec = kYb + 2 * kTileBytes;     // 2 x (lse2[128], D[128]) fp32
   static constexpr int kBar = kVec + 2 * 1024;
-  static constexpr int kTotal = kBar + 256 + 1024;
+  static constexpr int kTotal = kBar + 192;
 };
+static_assert(BwdSmem::kTotal <= 232448, "shared memory budget");
 
 __device__ __forceinline__ void tma_load_5d_b(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
                                               int c0, int c1, int c2, int c3, int c4) {
@@ -166,19 +175,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 __nv_bfloat16* __restrict__ g0, __nv_bfloat16* __restrict__ g1, long long o_ss,
                 long long o_sb, long long o_sg, long long o_sj, int sq, int sk, int s_pad, int B,
                 int G, int qpg, float scale, int causal, int nsplit, float* __restrict__ kv_acc) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~static_cast<uintptr_t>(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) asm volatile("trap;");   // swizzled tiles need it
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::kBar);
   uint64_t* x_full = bars + 0;
-  uint64_t* y_full = bars + 1;    // [2]
-  uint64_t* y_empty = bars + 3;   // [2]
-  uint64_t* s_full = bars + 5;    // [2]
-  uint64_t* dp_full = bars + 7;
-  uint64_t* p_ready = bars + 8;
-  uint64_t* ds_ready = bars + 9;
-  uint64_t* acc_done = bars + 10;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* ya_full = bars + 1;    // [3]
+  uint64_t* ya_empty = bars + 4;   // [3]
+  uint64_t* yb_full = bars + 7;    // [2]
+  uint64_t* yb_empty = bars + 9;   // [2]
+  uint64_t* vec_empty = bars + 11; // [2] math warps are done with the stage's LSE / D vectors
+  uint64_t* s_full = bars + 13;    // [2]
+  uint64_t* dp_full = bars + 15;
+  uint64_t* p_ready = bars + 16;
+  uint64_t* ds_ready = bars + 17;
+  uint64_t* acc_done = bars + 18;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int np = G * qpg;
@@ -214,9 +226,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmdO);
     mbar_init(x_full, 1);
+    for (int i = 0; i < 3; ++i) {
+      mbar_init(&ya_full[i], 1);
+      mbar_init(&ya_empty[i], 1);
+    }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&y_full[i], 1);
-      mbar_init(&y_empty[i], 1);
+      mbar_init(&yb_full[i], 1);
+      mbar_init(&yb_empty[i], 1);
+      mbar_init(&vec_empty[i], 256);
       mbar_init(&s_full[i], 1);
     }
     mbar_init(dp_full, 1);
@@ -257,30 +274,37 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tma_load_4d(sXb + kBoxBytes, &tmdO, x_full, 64, xblk * kBwdT, head, b);
       }
       for (int it = 0; it < n_iter; ++it) {
-        const int st = it & 1;
-        mbar_wait(&y_empty[st], ((it >> 1) & 1) ^ 1);
-        uint8_t* sYa = smem + BwdSmem::kY + st * 2 * kTileBytes;
-        uint8_t* sYb = sYa + kTileBytes;
+        const int sa = it % 3, sb = it & 1;
+        const uint32_t pha = ((it / 3) & 1) ^ 1, phb = ((it >> 1) & 1) ^ 1;
+        uint8_t* sYa = smem + BwdSmem::kYa + sa * kTileBytes;
+        uint8_t* sYb = smem + BwdSmem::kYb + sb * kTileBytes;
         if (kIsKV) {
           const int jl = it / y_count, yb = y_first + it - jl * y_count;
           const int jj = jj0 + jl;
           const int hd = g * qpg + jj;
-          float* vec = reinterpret_cast<float*>(smem + BwdSmem::kVec + st * 1024);
+          float* vec = reinterpret_cast<float*>(smem + BwdSmem::kVec + sb * 1024);
           const size_t voff = ((size_t)b * np + hd) * s_pad + (size_t)yb * kBwdT;
-          mbar_expect_tx(&y_full[st], 2 * kTileBytes + 1024);
-          tma_load_5d_b(sYa, &tmQ, &y_full[st], 0, yb * kBwdT, jj, g, b);
-          tma_load_5d_b(sYa + kBoxBytes, &tmQ, &y_full[st], 64, yb * kBwdT, jj, g, b);
-          tma_load_4d(sYb, &tmdO, &y_full[st], 0, yb * kBwdT, hd, b);
-          tma_load_4d(sYb + kBoxBytes, &tmdO, &y_full[st], 64, yb * kBwdT, hd, b);
-          bulk_load_1d(vec, lse2 + voff, 512, &y_full[st]);
-          bulk_load_1d(vec + 128, dvec + voff, 512, &y_full[st]);
+          mbar_wait(&ya_empty[sa], pha);
+          mbar_expect_tx(&ya_full[sa], kTileBytes);
+          tma_load_5d_b(sYa, &tmQ, &ya_full[sa], 0, yb * kBwdT, jj, g, b);
+          tma_load_5d_b(sYa + kBoxBytes, &tmQ, &ya_full[sa], 64, yb * kBwdT, jj, g, b);
+          mbar_wait(&yb_empty[sb], phb);
+          mbar_wait(&vec_empty[sb], phb);
+          mbar_expect_tx(&yb_full[sb], kTileBytes + 1024);
+          tma_load_4d(sYb, &tmdO, &yb_full[sb], 0, yb * kBwdT, hd, b);
+          tma_load_4d(sYb + kBoxBytes, &tmdO, &yb_full[sb], 64, yb * kBwdT, hd, b);
+          bulk_load_1d(vec, lse2 + voff, 512, &yb_full[sb]);
+          bulk_load_1d(vec + 128, dvec + voff, 512, &yb_full[sb]);
         } else {
           const int yb = y_first + it;
-          mbar_expect_tx(&y_full[st], 2 * kTileBytes);
-          tma_load_4d(sYa, &tmK, &y_full[st], 0, yb * kBwdT, g, b);
-          tma_load_4d(sYa + kBoxBytes, &tmK, &y_full[st], 64, yb * kBwdT, g, b);
-          tma_load_4d(sYb, &tmV, &y_full[st], 0, yb * kBwdT, g, b);
-          tma_load_4d(sYb + kBoxBytes, &tmV, &y_full[st], 64, yb * kBwdT, g, b);
+          mbar_wait(&ya_empty[sa], pha);
+          mbar_expect_tx(&ya_full[sa], kTileBytes);
+          tma_load_4d(sYa, &tmK, &ya_full[sa], 0, yb * kBwdT, g, b);
+          tma_load_4d(sYa + kBoxBytes, &tmK, &ya_full[sa], 64, yb * kBwdT, g, b);
+          mbar_wait(&yb_empty[sb], phb);
+          mbar_expect_tx(&yb_full[sb], kTileBytes);
+          tma_load_4d(sYb, &tmV, &yb_full[sb], 0, yb * kBwdT, g, b);
+          tma_load_4d(sYb + kBoxBytes, &tmV, &yb_full[sb], 64, yb * kBwdT, g, b);
         }
       }
     }
@@ -290,7 +314,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       constexpr uint32_t idesc_ss = make_idesc_bf16(kBwdT, kBwdT, 0, 0);
       constexpr uint32_t idesc_ts = make_idesc_bf16(kBwdT, kBwdT, 0, 1);
       const uint32_t aXa = smem_u32(sXa), aXb = smem_u32(sXb);
-      const uint32_t aY = smem_u32(smem + BwdSmem::kY);
+      const uint32_t aYa = smem_u32(smem + BwdSmem::kYa), aYb = smem_u32(smem + BwdSmem::kYb);
       // D = X * Y^T, both K-major with the head dim split into two 64-wide boxes
       auto mma_xyT = [&](uint32_t d, uint32_t x, uint32_t y) {
 #pragma unroll
@@ -310,62 +334,67 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                        (first && k == 0) ? 0u : 1u);
         }
       };
+      auto ya_addr = [&](int it) { return aYa + (it % 3) * kTileBytes; };
+      auto yb_addr = [&](int it) { return aYb + (it & 1) * kTileBytes; };
+      auto wait_ya = [&](int it) { mbar_wait(&ya_full[it % 3], (it / 3) & 1); };
+      auto wait_yb = [&](int it) { mbar_wait(&yb_full[it & 1], (it >> 1) & 1); };
       mbar_wait(x_full, 0);
-      mbar_wait(&y_full[0], 0);
+      wait_ya(0);
       tc_fence_after();
+      mma_xyT(tm_A, aXa, ya_addr(0));
+      umma_commit(&s_full[0]);
+      wait_yb(0);
+      tc_fence_after();
+      mma_xyT(tm_B, aXb, yb_addr(0));
+      umma_commit(dp_full);
       if (kIsKV) {
-        mma_xyT(tm_A, aXa, aY);
-        umma_commit(&s_full[0]);
-        mma_xyT(tm_B, aXb, aY + kTileBytes);
-        umma_commit(dp_full);
         for (int it = 0; it < n_iter; ++it) {
-          const int st = it & 1;
-          const uint32_t ya = aY + st * 2 * kTileBytes, yb = ya + kTileBytes;
           mbar_wait(p_ready, it & 1);
           tc_fence_after();
-          mma_tmem_y(tm_acc1, tm_A, yb, it == 0);            // dV += P^T dO
+          mma_tmem_y(tm_acc1, tm_A, yb_addr(it), it == 0);   // dV += P^T dO
+          umma_commit(&yb_empty[it & 1]);                     // dO_i: last use
           if (it + 1 < n_iter) {
-            mbar_wait(&y_full[st ^ 1], ((it + 1) >> 1) & 1);
+            wait_ya(it + 1);
             tc_fence_after();
-            mma_xyT(tm_A, aXa, aY + (st ^ 1) * 2 * kTileBytes);
+            mma_xyT(tm_A, aXa, ya_addr(it + 1));
             umma_commit(&s_full[0]);
           }
           mbar_wait(ds_ready, it & 1);
           tc_fence_after();
-          mma_tmem_y(tm_acc2, tm_B, ya, it == 0);            // dK += dS^T Q
-          umma_commit(&y_empty[st]);
+          mma_tmem_y(tm_acc2, tm_B, ya_addr(it), it == 0);   // dK += dS^T Q
+          umma_commit(&ya_empty[it % 3]);                     // Q_i: last use
           if (it + 1 < n_iter) {
-            mma_xyT(tm_B, aXb, aY + (st ^ 1) * 2 * kTileBytes + kTileBytes);
+            wait_yb(it + 1);
+            tc_fence_after();
+            mma_xyT(tm_B, aXb, yb_addr(it + 1));
             umma_commit(dp_full);
           }
         }
       } else {
-        mma_xyT(tm_A, aXa, aY);
-        umma_commit(&s_full[0]);
-        mma_xyT(tm_B, aXb, aY + kTileBytes);
-        umma_commit(dp_full);
+        umma_commit(&yb_empty[0]);                            // V_0 is only read by dP(0)
         if (n_iter > 1) {
-          mbar_wait(&y_full[1], 0);
+          wait_ya(1);
           tc_fence_after();
-          mma_xyT(tm_A + 128, aXa, aY + 2 * kTileBytes);
+          mma_xyT(tm_A + 128, aXa, ya_addr(1));
           umma_commit(&s_full[1]);
         }
         for (int it = 0; it < n_iter; ++it) {
-          const int st = it & 1;
-          const uint32_t ya = aY + st * 2 * kTileBytes;
           mbar_wait(ds_ready, it & 1);
           tc_fence_after();
-          mma_tmem_y(tm_acc2, tm_B, ya, it == 0);            // dQ += dS K
-          umma_commit(&y_empty[st]);
+          mma_tmem_y(tm_acc2, tm_B, ya_addr(it), it == 0);   // dQ += dS K
+          umma_commit(&ya_empty[it % 3]);                     // K_j: last use
           if (it + 1 < n_iter) {
-            mma_xyT(tm_B, aXb, aY + (st ^ 1) * 2 * kTileBytes + kTileBytes);
+            wait_yb(it + 1);
+            tc_fence_after();
+            mma_xyT(tm_B, aXb, yb_addr(it + 1));
             umma_commit(dp_full);
+            umma_commit(&yb_empty[(it + 1) & 1]);             // V_{j+1}: only read by dP
           }
           if (it + 2 < n_iter) {
-            mbar_wait(&y_full[st], ((it + 2) >> 1) & 1);
+            wait_ya(it + 2);
             tc_fence_after();
-            mma_xyT(tm_A + st * 128, aXa, ya);
-            umma_commit(&s_full[st]);
+            mma_xyT(tm_A + (it & 1) * 128, aXa, ya_addr(it + 2));
+            umma_commit(&s_full[it & 1]);
           }
         }
       }
@@ -390,7 +419,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (kIsKV) {
         const int jj = it / y_count;
         yb = y_first + it - jj * y_count;
-        mbar_wait(&y_full[st], (it >> 1) & 1);  // LSE / D vectors of this stage
+        mbar_wait(&yb_full[st], (it >> 1) & 1);  // LSE / D vectors travel with the dO stage
       } else {
         yb = y_first + it;
       }
@@ -458,6 +487,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tmem_st_wait_b();
       tc_fence_before();
       mbar_arrive(ds_ready);
+      if (kIsKV) mbar_arrive(&vec_empty[st]);      // this stage's LSE / D vectors may be overwritten
     }
     // ------------------------------ epilogue ----------------------------------
     if (n_iter > 0) {

@@ -34,7 +34,9 @@ MODELS = {
 }
 
 
-def parallel_layout(n_gpus, model):
+def parallel_layout(n_gpus, model, tp_override=0):
+    if tp_override:
+        return tp_override, n_gpus // tp_override
     if model == "tiny":
         return (1, n_gpus) if n_gpus < 2 else (2, n_gpus // 2)
     tp = 1 if n_gpus == 1 else 2
@@ -48,6 +50,7 @@ def build_arg_list(a, tp, dp):
     gbs = a.micro_batch * a.num_microbatches * dp
     argv = [
         "--b200_kernels", getattr(a, 'kernels', 'auto'), "--b200_fused_comm", getattr(a, 'fused_comm', 'auto'),
+        "--b200_fused_dp", getattr(a, 'fused_dp', 'auto'),
         "--model_name", "llama2", "--num_layers", str(L), "--hidden_size", str(h),
         "--num_attention_heads", str(nh), "--num_attention_heads_kv", str(nkv),
         "--ffn_hidden_size", str(ffn), "--seq_length", str(a.seq), "--max_position_embeddings", str(a.seq),
@@ -119,7 +122,7 @@ def run_ours(a):
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
-    tp, dp = parallel_layout(a.gpus, a.model)
+    tp, dp = parallel_layout(a.gpus, a.model, getattr(a, 'tp', 0))
     argv, gbs = build_arg_list(a, tp, dp)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29400")
@@ -282,7 +285,7 @@ def run_reference(a):
                 print(json.dumps({"impl": "reference", "unavailable":
                                   "reference sources not present under baseline/_ref: " + r.stderr[-200:]}))
             return 0
-    tp, dp = parallel_layout(a.gpus, a.model)
+    tp, dp = parallel_layout(a.gpus, a.model, getattr(a, 'tp', 0))
     cmd = [sys.executable, script, "--model", a.model, "--gpus", str(a.gpus), "--steps", str(a.steps),
            "--warmup", str(a.warmup), "--seq", str(a.seq), "--micro_batch", str(a.micro_batch),
            "--num_microbatches", str(a.num_microbatches), "--tp", str(tp), "--dp", str(dp),
@@ -299,6 +302,7 @@ def main():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--model", default="llama2-7b", choices=list(MODELS))
+    p.add_argument("--tp", type=int, default=0, help="A/B only: override the tensor-parallel size (default: 2 for N>=2)")
     p.add_argument("--seq", type=int, default=4096)
     p.add_argument("--micro_batch", type=int, default=1)
     p.add_argument("--num_microbatches", type=int, default=4)
@@ -307,6 +311,7 @@ def main():
     p.add_argument("--debug_layers", type=int, default=0, help="debug only: override the layer count")
     p.add_argument("--kernels", default="auto", help="debug only: auto|off")
     p.add_argument("--fused_comm", default="auto", help="A/B only: auto|on|off (in-kernel TP collectives)")
+    p.add_argument("--fused_dp", default="auto", help="A/B only: auto|on|off (in-kernel DP reduce-scatter/all-gather)")
     p.add_argument("--torch_profile", action="store_true", help="also write gpurun_out/torch_profile_nN.md")
     p.add_argument("--profile", action="store_true", help="1 warm-up + K steps, no e2e region; for ncu, NOT a bench value")
     a = p.parse_args()

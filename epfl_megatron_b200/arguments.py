@@ -216,6 +216,7 @@ _GROUPS = {
         ("--b200_kernels", dict(default="auto", choices=["auto", "on", "off"])),
         ("--b200_gemm", dict(default="auto", choices=["auto", "own", "cublas"])),
         ("--b200_fused_comm", dict(default="auto", choices=["auto", "on", "off"])),
+        ("--b200_fused_dp", dict(default="auto", choices=["auto", "on", "off"])),
         ("--ddp_bucket_mb", dict(type=float, default=256)),
         ("--no_overlap_grad_reduce", dict(action=F, dest="overlap_grad_reduce")),
         ("--log_throughput", dict(action=T)), ("--metrics_jsonl", dict(type=str)),

@@ -35,9 +35,14 @@ def default_param_group_key(name, param):
 
 
 class MemoryBuffer:
-    def __init__(self, numel, numel_padded, dtype, device):
+    def __init__(self, numel, numel_padded, dtype, device, symmetric=False):
         self.numel, self.numel_padded, self.dtype = numel, numel_padded, dtype
-        self.data = torch.zeros(numel_padded, dtype=dtype, device=device, requires_grad=False)
+        if symmetric:
+            # own cudaMalloc allocation that the data-parallel peers map (parallel/dp_symm.py)
+            from ..parallel.dp_symm import symm_tensor
+            self.data = symm_tensor(numel_padded, dtype, device)
+        else:
+            self.data = torch.zeros(numel_padded, dtype=dtype, device=device, requires_grad=False)
 
     def zero(self):
         self.data.zero_()
@@ -71,19 +76,24 @@ class DistributedDataParallelBase(MegatronModule, ABC):
 
 
 class _Bucket:
-    __slots__ = ("dtype", "start", "end", "params", "pending", "early_ok", "launched")
+    __slots__ = ("dtype", "start", "end", "params", "pending", "early_ok", "launched", "index")
 
-    def __init__(self, dtype, start):
-        self.dtype, self.start, self.end = dtype, start, start
+    def __init__(self, dtype, start, index=0):
+        self.dtype, self.start, self.end, self.index = dtype, start, start, index
         self.params, self.pending, self.early_ok, self.launched = [], 0, True, False
 
 
 class DistributedDataParallel(DistributedDataParallelBase):
     def __init__(self, module, accumulate_allreduce_grads_in_fp32, use_contiguous_buffers,
                  fuse_wgrad: bool = True, group_key_fn=None, overlap_grad_reduce: bool = False,
-                 bucket_mb: float = 256.0):
+                 bucket_mb: float = 256.0, fused_dp: bool = False):
         super().__init__(module)
         self.overlap_grad_reduce = overlap_grad_reduce
+        # fp32 buffers live in peer-mappable memory; the distributed optimizer attaches a
+        # DPWorkspace per buffer and the reduction becomes the in-kernel reduce-scatter
+        self.fused_dp = fused_dp
+        self._dp_ws = {}
+        self._reduced = False
         self.bucket_bytes = int(bucket_mb * (1 << 20))
         self._buckets, self._bucket_of, self._arrivals, self._expected = [], {}, {}, 0
         self._handles = []
@@ -132,7 +142,8 @@ class DistributedDataParallel(DistributedDataParallelBase):
         for dt in list(sizes):
             n = cursor[dt]
             unit = dp * 8
-            self._grad_buffers[dt] = MemoryBuffer(n, unit * int(math.ceil(n / unit)), dt, dev)
+            self._grad_buffers[dt] = MemoryBuffer(n, unit * int(math.ceil(n / unit)), dt, dev,
+                                                  symmetric=fused_dp and dt == torch.float and dp > 1)
             # a group range is extended to the start of the next group so ranges tile the buffer
             ordered = sorted(self.group_ranges[dt].items(), key=lambda kv: kv[1][0])
             for j, (key, (lo, hi)) in enumerate(ordered):
@@ -172,9 +183,10 @@ class DistributedDataParallel(DistributedDataParallelBase):
         for dt, items in self.layout.items():
             esz = self._grad_buffers[dt].data.element_size()
             cur = None
+            first = len(self._buckets)
             for p, start, end, _ in items:
                 if cur is None:
-                    cur = _Bucket(dt, start)
+                    cur = _Bucket(dt, start, len(self._buckets) - first)
                     self._buckets.append(cur)
                 cur.params.append(p)
                 cur.end = end
@@ -199,11 +211,23 @@ class DistributedDataParallel(DistributedDataParallelBase):
             return
         b = self._bucket_of[p]
         b.pending -= 1
-        if b.pending == 0 and b.early_ok and not b.launched:
+        if b.pending == 0 and b.early_ok and not b.launched and self.overlap_grad_reduce:
             self._launch(b, async_op=True)
+
+    def buckets_of(self, dtype):
+        return [b for b in self._buckets if b.dtype == dtype]
+
+    def attach_dp_workspace(self, dtype, ws):
+        """Called by the distributed optimizer: buckets of this buffer are reduce-scattered by
+        parallel/dp_symm.DPWorkspace (only the owner's shard ends up averaged)."""
+        self._dp_ws[dtype] = ws
 
     def _launch(self, b, async_op):
         b.launched = True
+        ws = self._dp_ws.get(b.dtype)
+        if ws is not None:
+            ws.reduce_bucket(b.index, b.start, b.end, overlapped=async_op)
+            return
         view = self._grad_buffers[b.dtype].data[b.start:b.end]
         grp = mpu.get_data_parallel_group()
         avg = dist.ReduceOp.AVG if view.is_cuda else dist.ReduceOp.SUM
@@ -218,14 +242,17 @@ class DistributedDataParallel(DistributedDataParallelBase):
         when this wrapper averaged its whole buffer over the data-parallel group (the optimizer
         then skips its own reduction), False when overlap is off."""
         if not self._expected:
-            return False
+            return self._reduced
         for b in self._buckets:
             if not b.launched:
                 self._launch(b, async_op=False)
         for h in self._handles:
             h.wait()
         self._handles = []
+        for ws in self._dp_ws.values():
+            ws.finish()
         self._expected = 0
+        self._reduced = True
         return True
 
     def zero_grad_buffer(self):
@@ -234,13 +261,16 @@ class DistributedDataParallel(DistributedDataParallelBase):
         for p in self._params:
             p._b200_main_grad_empty = True
         self._expected = 0
-        if self.overlap_grad_reduce and self._buckets and mpu.get_data_parallel_world_size() > 1 \
-                and dist.is_initialized():
+        self._reduced = False
+        if (self.overlap_grad_reduce or self._dp_ws) and self._buckets and dist.is_initialized() \
+                and mpu.get_data_parallel_world_size() > 1:
             from .. import global_vars
             self._expected = global_vars.get_num_microbatches()
             self._arrivals = {}
             for b in self._buckets:
                 b.pending, b.launched = len(b.params), False
+            for ws in self._dp_ws.values():
+                ws.new_step()
 
     def finalize_grad_buffer(self):
         """Physically zero the slices that received no gradient this step."""

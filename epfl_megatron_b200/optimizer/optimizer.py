@@ -68,8 +68,17 @@ class _Chunk:
         self.shard_lo, self.shard_hi = r * (self.N // dp), (r + 1) * (self.N // dp)
         n = self.shard_hi - self.shard_lo
         pdtype = self.layout[0][0].dtype
+        # fused data-parallel path (parallel/dp_symm.py): gradient and parameter buffers are mapped
+        # by the peers, which pull gradient slices and push parameter shards from inside kernels
+        self.ws = None
+        fused = (distributed and dp > 1 and getattr(ddp, "fused_dp", False) and dtype == torch.float
+                 and pdtype == torch.bfloat16 and hasattr(self.grad, "_b200_symm_base"))
         # parameter buffer: the model parameters become views into it
-        self.param = torch.zeros(self.N, dtype=pdtype, device=dev)
+        if fused:
+            from ..parallel.dp_symm import DPWorkspace, symm_tensor
+            self.param = symm_tensor(self.N, pdtype, dev)
+        else:
+            self.param = torch.zeros(self.N, dtype=pdtype, device=dev)
         for p, s, e, _ in self.layout:
             self.param[s:e].copy_(p.data.reshape(-1))
             p.data = self.param[s:e].view(p.data.shape)
@@ -80,6 +89,10 @@ class _Chunk:
             self.main = self.param[self.shard_lo:self.shard_hi]
         self.m = torch.zeros(n, dtype=torch.float32, device=dev)
         self.v = torch.zeros(n, dtype=torch.float32, device=dev)
+        if fused:
+            self.ws = DPWorkspace(mpu.get_data_parallel_group(), self.grad, self.param,
+                                  len(ddp.buckets_of(dtype)))
+            ddp.attach_dp_workspace(dtype, self.ws)
 
     def local(self, lo, hi):
         """Intersection of [lo, hi) with the owned shard, in shard-local coordinates."""
@@ -156,6 +169,8 @@ class FlatOptimizer(MegatronOptimizer):
         self._skip = torch.zeros(1, dtype=torch.float32, device=dev)
         self._norm_out = torch.zeros(2, dtype=torch.float32, device=dev)
         self._use_kernels = dev.type == "cuda" and L.available()
+        # Adam writes the bf16 shard into every rank's parameter buffer (fused all-gather)
+        self._push_params = self.kind == "adam" and any(ch.ws is not None for ch in self.chunks)
         if self._use_kernels:
             self._sumsq_scratch = torch.empty(L.lib().b200_sumsq_scratch_elems(), dtype=torch.float32,
                                               device=dev)
@@ -242,11 +257,20 @@ class FlatOptimizer(MegatronOptimizer):
             dist.all_reduce(w.main_grad, group=mpu.get_position_embedding_group())
 
     def reduce_model_grads(self, args, timers):
-        timers("layernorm-grads-all-reduce", log_level=1).start(barrier=args.barrier_with_L1_time)
+        # Order: (1) tied-embedding all-reduces over the pipeline ends, on gradients no bucket has
+        # touched yet (buckets holding shared parameters are never launched early) -- they must see
+        # whole gradients, and a reduce-scatter leaves only the owner's shard valid; (2) the
+        # data-parallel reduction, which also waits for the buckets launched under backward;
+        # (3) the tensor-parallel all-reduce of the sequence-parallel norm gradients: all ranks of
+        # a TP group own the same shard range, and doing it after (2) keeps it from racing with
+        # bucket reductions still in flight. Sums commute, the result equals the reference's
+        # layernorm -> embedding -> data-parallel order (optimizer.py:280-301).
         for ch in self.chunks:
             ch.ddp.finalize_grad_buffer()
-        self.allreduce_layernorm_grads(args)
-        timers("layernorm-grads-all-reduce").stop()
+        timers("embedding-grads-all-reduce", log_level=1).start(barrier=args.barrier_with_L1_time)
+        self.allreduce_word_embedding_grads(args)
+        self.allreduce_position_embedding_grads(args)
+        timers("embedding-grads-all-reduce").stop()
         timers("grads-reduce", log_level=1).start(barrier=args.barrier_with_L1_time)
         dp = mpu.get_data_parallel_world_size()
         if dp > 1:
@@ -263,10 +287,9 @@ class FlatOptimizer(MegatronOptimizer):
                 else:
                     dist.all_reduce(ch.grad, group=grp)
         timers("grads-reduce").stop()
-        timers("embedding-grads-all-reduce", log_level=1).start(barrier=args.barrier_with_L1_time)
-        self.allreduce_word_embedding_grads(args)
-        self.allreduce_position_embedding_grads(args)
-        timers("embedding-grads-all-reduce").stop()
+        timers("layernorm-grads-all-reduce", log_level=1).start(barrier=args.barrier_with_L1_time)
+        self.allreduce_layernorm_grads(args)
+        timers("layernorm-grads-all-reduce").stop()
 
     def gather_model_params(self, args, timers):
         if not self.distributed or mpu.get_data_parallel_world_size() == 1:
@@ -274,7 +297,10 @@ class FlatOptimizer(MegatronOptimizer):
         timers("params-all-gather", log_level=1).start(barrier=args.barrier_with_L1_time)
         grp = mpu.get_data_parallel_group()
         for ch in self.chunks:
-            all_gather_into(ch.param, ch.param[ch.shard_lo:ch.shard_hi], grp)
+            if ch.ws is not None and self._push_params:
+                ch.ws.params_barrier()     # the Adam kernel already wrote every rank's copy
+            else:
+                all_gather_into(ch.param, ch.param[ch.shard_lo:ch.shard_hi], grp)
         timers("params-all-gather").stop()
 
     # ------------------------------------------------------------------ step
@@ -355,7 +381,12 @@ class FlatOptimizer(MegatronOptimizer):
         lr, wd = g["lr"], g["weight_decay"]
         b1, b2 = g["betas"]
         if self._use_kernels and n % 4 == 0:
-            if self.kind == "adam":
+            if self.kind == "adam" and ch.ws is not None and self._push_params:
+                assert n % 8 == 0 and (ch.shard_lo + lo) % 8 == 0
+                L.call("b200_adam_step_push", main.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(),
+                       ch.ws.param_dsts(ch.shard_lo + lo), ch.ws.dp, n, lr, b1, b2, g["eps"], wd,
+                       self.step_count, 1, 1, self._coef.data_ptr(), self._skip.data_ptr(), L.stream_ptr())
+            elif self.kind == "adam":
                 L.call("b200_adam_step", main.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(),
                        L.ptr(p16), n, lr, b1, b2, g["eps"], wd, self.step_count, 1, 1,
                        self._coef.data_ptr(), self._skip.data_ptr(), L.stream_ptr())

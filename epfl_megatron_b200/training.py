@@ -174,17 +174,38 @@ def get_model(model_provider_func, model_type=ModelType.encoder_or_decoder, wrap
         elif args.DDP_impl == "local":
             key_fn = make_group_key_fn(getattr(args, "_no_wd_cond", None), getattr(args, "_scale_lr_cond", None),
                                        getattr(args, "_lr_mult", 1.0))
+            fused_dp = _fused_dp_enabled(args, dev)
             model = [LocalDDP(m, args.accumulate_allreduce_grads_in_fp32,
                               args.use_contiguous_buffers_in_local_ddp,
                               fuse_wgrad=args.gradient_accumulation_fusion, group_key_fn=key_fn,
                               overlap_grad_reduce=getattr(args, "overlap_grad_reduce", True),
-                              bucket_mb=getattr(args, "ddp_bucket_mb", 256)) for m in model]
+                              bucket_mb=getattr(args, "ddp_bucket_mb", 256), fused_dp=fused_dp) for m in model]
             if args.data_parallel_random_init:
                 for m in model:
                     m.broadcast_params()
         else:
             raise NotImplementedError(f"Unknown DDP implementation specified: {args.DDP_impl}. Exiting.")
     return model
+
+
+def _fused_dp_enabled(args, dev) -> bool:
+    """--b200_fused_dp: in-kernel reduce-scatter / all-gather of the distributed optimizer over peer
+    memory (parallel/dp_symm.py). Needs bf16 parameters with fp32 gradient accumulation, Adam, and a
+    data-parallel group of 2..8 GPUs on one host. Collective over the data-parallel group."""
+    mode = getattr(args, "b200_fused_dp", "auto")
+    if mode == "off" or dev is None or args.distributed_backend == "gloo":
+        return False
+    from .ops import lib as _L
+    dp = mpu.get_data_parallel_world_size()
+    ok = (_L.available() and args.use_distributed_optimizer and 2 <= dp <= 8 and args.bf16
+          and args.accumulate_allreduce_grads_in_fp32 and args.optimizer == "adam")
+    if ok:
+        from .parallel.dp_symm import group_on_one_host
+        ok = group_on_one_host(mpu.get_data_parallel_group())
+    if mode == "on" and not ok:
+        raise RuntimeError("--b200_fused_dp on needs: CUDA kernels, --use_distributed_optimizer, --bf16 with fp32 "
+                           "gradient accumulation, Adam, 2..8 data-parallel ranks on one host")
+    return ok
 
 
 def _get_optimizer_param_scheduler(optimizer, args):

@@ -16,7 +16,7 @@ _ALIASES = {
     "optimizer_param_scheduler": "optimizer_param_scheduler", "timers": "timers", "utils": "utils",
     "memory": "memory", "dist_signal_handler": "dist_signal_handler", "wandb_logger": "wandb_logger",
     "optimizer": "optimizer", "optimizer.optimizer": "optimizer.optimizer",
-    "optimizer.distrib_optimizer": "optimizer.optimizer", "optimizer.clip_grads": "optimizer.clip_grads",
+    "optimizer.distrib_optimizer": "optimizer.distrib_optimizer", "optimizer.clip_grads": "optimizer.clip_grads",
     "optimizer.grad_scaler": "optimizer.grad_scaler",
     "model": "models", "model.enums": "models.enums", "model.transformer": "models.transformer",
     "model.language_model": "models.language_model", "model.gpt_model": "models.gpt_model",
@@ -51,6 +51,8 @@ _ALIASES = {
     "tokenizer.bert_tokenization": "tokenizer.bert_tokenization",
     "tokenizer.gpt2_tokenization": "tokenizer.gpt2_tokenization",
     "indexer": "indexer",
+    "fp16_deprecated": "fp16_deprecated", "fp16_deprecated.loss_scaler": "fp16_deprecated.loss_scaler",
+    "data.image_folder": "data.image_folder", "data.autoaugment": "data.autoaugment",
 }
 
 
@@ -78,30 +80,7 @@ core.tensor_parallel = sys.modules.get("megatron.core.tensor_parallel")
 core.utils = sys.modules.get("megatron.core.utils")
 mpu = core.mpu
 
-# legacy pickles reference these loss-scaler classes (megatron/fp16_deprecated/loss_scaler.py)
-_fp16 = types.ModuleType("megatron.fp16_deprecated")
-_ls = types.ModuleType("megatron.fp16_deprecated.loss_scaler")
-
-
-class LossScaler:
-    def __init__(self, scale=1):
-        self.cur_scale = scale
-
-
-class DynamicLossScaler:
-    def __init__(self, init_scale=2 ** 32, scale_factor=2.0, scale_window=1000, min_scale=1,
-                 delayed_shift=1, consecutive_hysteresis=False):
-        self.cur_scale, self.cur_iter, self.last_overflow_iter = init_scale, 0, -1
-        self.scale_factor, self.scale_window, self.min_scale = scale_factor, scale_window, min_scale
-        self.delayed_shift, self.cur_hysteresis = delayed_shift, delayed_shift
-        self.consecutive_hysteresis = consecutive_hysteresis
-
-
-_ls.LossScaler, _ls.DynamicLossScaler = LossScaler, DynamicLossScaler
-_fp16.loss_scaler = _ls
-sys.modules["megatron.fp16_deprecated"] = _fp16
-sys.modules["megatron.fp16_deprecated.loss_scaler"] = _ls
-fp16_deprecated = _fp16
+fp16_deprecated = sys.modules.get("megatron.fp16_deprecated")   # unpickling stubs for legacy checkpoints
 
 from epfl_megatron_b200 import (get_args, get_current_global_batch_size, get_num_microbatches,  # noqa: E402,F401
                                 get_signal_handler, get_tensorboard_writer, get_timers, get_tokenizer,

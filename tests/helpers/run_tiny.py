@@ -35,6 +35,7 @@ def main():
     p.add_argument("--no_overlap", action="store_true")
     p.add_argument("--bucket_mb", type=int, default=None)
     p.add_argument("--fused_comm", default="auto")
+    p.add_argument("--fused_dp", default="auto")
     a = p.parse_args()
 
     import torch
@@ -75,7 +76,7 @@ def main():
         argv.append("--no_overlap_grad_reduce")
     if a.bucket_mb is not None:
         argv += ["--ddp_bucket_mb", str(a.bucket_mb)]
-    argv += ["--b200_fused_comm", a.fused_comm]
+    argv += ["--b200_fused_comm", a.fused_comm, "--b200_fused_dp", a.fused_dp]
     if a.recompute:
         argv += ["--recompute_granularity", "full", "--recompute_method", "uniform"]
     if a.vpp_layers:
@@ -113,11 +114,16 @@ def main():
         norms.append(float(gn) if gn is not None else None)
     if a.save:
         save_checkpoint(args.iteration + a.steps, model, optimizer, sched)
+    fused_dp_used = False
+    for ch in getattr(optimizer, "chunks", []):
+        if getattr(ch, "ws", None) is not None:
+            ch.ws.check()          # raises if an in-kernel cross-GPU wait timed out
+            fused_dp_used = True
     sys.stdout = real
     import torch.distributed as dist
     if mpu.is_pipeline_last_stage(ignore_virtual=True) and mpu.get_tensor_model_parallel_rank() == 0 \
             and mpu.get_data_parallel_rank() == 0:
-        print("RESULT " + json.dumps({"losses": losses, "grad_norms": norms}), flush=True)
+        print("RESULT " + json.dumps({"losses": losses, "grad_norms": norms, "fused_dp": fused_dp_used}), flush=True)
     dist.barrier()
     dist.destroy_process_group()
 

@@ -1,0 +1,65 @@
+"""Small CPU-only pieces: the vestigial vision data utilities and the unpickling stubs."""
+import io
+import pickle
+import random
+
+import pytest
+
+
+def _write_images(root, classes=("ant", "bee"), per_class=3):
+    from PIL import Image
+    for ci, c in enumerate(classes):
+        d = root / c
+        d.mkdir()
+        for i in range(per_class):
+            Image.new("RGB", (24, 16), (40 * ci + 10, 20 * i, 200)).save(d / f"{i}.png")
+        (d / "notes.txt").write_text("not an image")
+
+
+def test_image_folder(tmp_path):
+    pytest.importorskip("PIL")
+    from epfl_megatron_b200.data.image_folder import ImageFolder, is_image_file
+    _write_images(tmp_path)
+    ds = ImageFolder(str(tmp_path))
+    assert ds.classes == ["ant", "bee"] and len(ds) == 6
+    img, target = ds[4]
+    assert img.size == (24, 16) and target == 1
+    assert is_image_file("x.JPG") and not is_image_file("x.txt")
+    half = ImageFolder(str(tmp_path), classes_fraction=0.5)
+    assert half.classes == ["ant"] and len(half) == 3
+    few = ImageFolder(str(tmp_path), data_per_class_fraction=0.34, transform=lambda im: im.size)
+    assert len(few) == 2 and few[0][0] == (24, 16)
+
+
+def test_autoaugment_policy():
+    pytest.importorskip("PIL")
+    from PIL import Image
+    from epfl_megatron_b200.data.autoaugment import ImageNetPolicy, SubPolicy
+    random.seed(3)
+    img = Image.new("RGB", (32, 32), (120, 30, 200))
+    pol = ImageNetPolicy()
+    assert len(pol.policies) == 25
+    for _ in range(60):
+        out = pol(img)
+        assert out.size == img.size and out.mode == "RGB"
+    # every operation runs at full probability
+    for op in ("shearX", "shearY", "translateX", "translateY", "rotate", "color", "posterize", "solarize",
+               "contrast", "sharpness", "brightness", "autocontrast", "equalize", "invert"):
+        assert SubPolicy(op, 1.0, 9, "invert", 0.0, 0)(img).size == img.size
+    with pytest.raises(ValueError):
+        SubPolicy("blur", 0.5, 1, "invert", 0.5, 1)
+
+
+def test_deprecated_loss_scaler_unpickles_under_reference_path():
+    import megatron  # noqa: F401  (installs the megatron.* aliases)
+    from megatron.fp16_deprecated.loss_scaler import DynamicLossScaler, LossScaler
+    assert DynamicLossScaler.__module__.endswith("fp16_deprecated.loss_scaler")
+    blob = pickle.dumps({"a": LossScaler(4.0), "b": DynamicLossScaler(init_scale=8)})
+    back = pickle.load(io.BytesIO(blob))
+    assert back["a"].cur_scale == 4.0 and back["b"].cur_scale == 8
+
+
+def test_distrib_optimizer_module_path():
+    from megatron.optimizer.distrib_optimizer import DistributedOptimizer, Range
+    r = Range(8, 24).normalize(100)
+    assert (r.start, r.end, r.size) == (100, 116, 16) and DistributedOptimizer.__name__ == "DistributedOptimizer"

@@ -37,6 +37,27 @@ def test_dp2_distributed_optimizer(single):
     assert r["losses"][-1] < r["losses"][0]
 
 
+def test_dp2_fused_reduce_scatter_and_param_push():
+    """In-kernel reduce-scatter + Adam-with-all-gather (parallel/dp_symm.py) against the NCCL path:
+    same losses and gradient norms, with several buckets overlapped with backward."""
+    _need(2)
+    kw = dict(nproc=2, steps=6, dist_opt=True, num_microbatches=2, bucket_mb=1, layers=4)
+    fused = run_tiny(fused_dp="on", **kw)
+    nccl = run_tiny(fused_dp="off", **kw)
+    assert fused["fused_dp"] and not nccl["fused_dp"]
+    _close(fused["losses"], nccl["losses"], 2e-3)
+    _close(fused["grad_norms"], nccl["grad_norms"], 5e-3)
+
+
+def test_dp4_fused_with_tp2():
+    _need(8)
+    kw = dict(nproc=8, tp=2, steps=5, dist_opt=True, num_microbatches=2, bucket_mb=1, layers=4)
+    fused = run_tiny(fused_dp="on", **kw)
+    nccl = run_tiny(fused_dp="off", **kw)
+    assert fused["fused_dp"]
+    _close(fused["losses"], nccl["losses"], 5e-3)
+
+
 def test_pp2_1f1b(single):
     _need(2)
     r = run_tiny(nproc=2, pp=2, steps=5, num_microbatches=4)

@@ -65,7 +65,7 @@ dp_reduce_kernel(DpSrc src, int rank, float4* out, long long n_vec, float scale,
   if (threadIdx.x < kDp && threadIdx.x != rank) dp_spin(ready + threadIdx.x, epoch, 1u, threadIdx.x);
   __syncthreads();
   const long long stride = (long long)gridDim.x * blockDim.x;
-  constexpr int kU = kDp <= 2 ? 4 : 2;       // 16-byte loads in flight per thread: kU * kDp
+  constexpr int kU = kDp <= 2 ? 8 : (kDp <= 4 ? 4 : 2);   // 16-byte loads in flight per thread: kU * kDp
   long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   for (; i + (kU - 1) * stride < n_vec; i += kU * stride) {
     float4 v[kU][kDp];
@@ -211,6 +211,12 @@ B200_API int b200_dp_wait(const unsigned* flags, int n, int skip, unsigned value
   dp_wait_kernel<<<1, 32, 0, stream>>>(flags, n, skip, value, site);
   B200_CHECK_LAUNCH();
   return 0;
+}
+
+// Stream-ordered copy through the copy engines (src may be a peer-mapped address): moves a peer's
+// gradient slice into local staging without occupying SMs while the backward pass computes.
+B200_API int b200_copy_async(void* dst, const void* src, long long bytes, cudaStream_t stream) {
+  return (int)cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, stream);
 }
 
 // Copies and clears the first timed-out wait (all zero: none). Synchronises the device.

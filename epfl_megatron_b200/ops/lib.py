@@ -70,6 +70,7 @@ _SIGNATURES = {
     "b200_adam_step_push": ([vp, vp, vp, vp, vp, i32, i64, f32, f32, f32, f32, f32, i32, i32, i32, vp, vp, vp], i32),
     "b200_dp_wait": ([vp, i32, i32, C.c_uint, C.c_uint, vp], i32),
     "b200_dp_debug_read": ([vp], i32),
+    "b200_copy_async": ([vp, vp, i64, vp], i32),
     "b200_gemm_rs_arrivals": ([i32, i32], i32),
     "b200_gemm_allgather": ([vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp], i32),
     "b200_gemm_reduce_scatter": ([vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp], i32),

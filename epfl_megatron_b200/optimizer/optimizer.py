@@ -90,8 +90,9 @@ class _Chunk:
         self.m = torch.zeros(n, dtype=torch.float32, device=dev)
         self.v = torch.zeros(n, dtype=torch.float32, device=dev)
         if fused:
-            self.ws = DPWorkspace(mpu.get_data_parallel_group(), self.grad, self.param,
-                                  len(ddp.buckets_of(dtype)))
+            bks = ddp.buckets_of(dtype)
+            self.ws = DPWorkspace(mpu.get_data_parallel_group(), self.grad, self.param, len(bks),
+                                  max(b.end - b.start for b in bks))
             ddp.attach_dp_workspace(dtype, self.ws)
 
     def local(self, lo, hi):

@@ -21,6 +21,7 @@ bucket of step e+1 before every owner has pulled step e (the next forward waits 
 from __future__ import annotations
 
 import ctypes as C
+import os
 import socket
 
 import torch
@@ -70,7 +71,7 @@ def _exchange(group, ptr: int):
 class DPWorkspace:
     """grad: fp32 [N] and param: bf16 [N], both from ``symm_tensor``; shard r = [r*N/dp, (r+1)*N/dp)."""
 
-    def __init__(self, group, grad: torch.Tensor, param: torch.Tensor, n_buckets: int):
+    def __init__(self, group, grad: torch.Tensor, param: torch.Tensor, n_buckets: int, max_bucket: int = 0):
         self.group = group
         self.dp = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
@@ -89,8 +90,14 @@ class DPWorkspace:
         self.epoch = 0          # one per training step (bucket flags)
         self.param_epoch = 0    # one per successful optimizer step
         self.side = torch.cuda.Stream(device=self.device)
-        self.blocks_overlap = 24
+        self.blocks_overlap = int(os.environ.get("B200_DP_BLOCKS", "96"))
         self.blocks_exposed = 148 * 4
+        self.allow_overlap = os.environ.get("B200_DP_NO_OVERLAP", "0") != "1"
+        # how an overlapped bucket travels: "ce" = copy engines into local staging + local reduce
+        # kernel (no SMs taken from the GEMMs), "pull" = peer loads inside the reduce kernel
+        self.overlap_mode = os.environ.get("B200_DP_OVERLAP_MODE", "ce")
+        self.max_bucket = min(max_bucket, self.shard) if max_bucket else self.shard
+        self._stage = None
         self._pending = False
 
     # ---- gradients -------------------------------------------------------------------------
@@ -100,6 +107,7 @@ class DPWorkspace:
     def reduce_bucket(self, index: int, start: int, end: int, overlapped: bool):
         """Announce bucket [start, end) and reduce the part of it this rank owns."""
         main = torch.cuda.current_stream()
+        overlapped = overlapped and self.allow_overlap
         if overlapped:
             self.side.wait_stream(main)
             stream = self.side
@@ -124,6 +132,17 @@ class DPWorkspace:
             grads = (C.c_void_p * 8)()
             for r in range(dp):
                 grads[r] = self.peer_grad[r] + 4 * lo
+            if overlapped and self.overlap_mode == "ce":
+                if self._stage is None:
+                    self._stage = torch.empty(dp - 1, self.max_bucket, dtype=torch.float32, device=self.device)
+                assert hi - lo <= self.max_bucket
+                L.call("b200_dp_wait", self.flags.data_ptr() + 4 * word, dp, me, self.epoch & 0xFFFFFFFF, 1, st)
+                i = 0
+                for r in range(dp):
+                    if r != me:
+                        L.call("b200_copy_async", self._stage[i].data_ptr(), grads[r], 4 * (hi - lo), st, launches=0)
+                        grads[r] = self._stage[i].data_ptr()
+                        i += 1
             L.call("b200_dp_reduce", grads, dp, me, hi - lo, 1.0 / dp, self.flags.data_ptr() + 4 * word,
                    self.epoch & 0xFFFFFFFF, self.blocks_overlap if overlapped else self.blocks_exposed, st)
 

@@ -22,31 +22,57 @@ __global__ void __launch_bounds__(256)
 rope_kernel(__nv_bfloat16* __restrict__ x, const float2* __restrict__ table,
             const long long* __restrict__ pos_ids, int S, int B, int G, int nslot, int nrot,
             int HN, int pos_offset, int max_pos, float sign, long long total_vec) {
+  // One thread owns one 16-byte column (4 rotation pairs) of one token and walks all rotated
+  // heads of that token: position lookup and the (cos, sin) values are loaded once and reused
+  // G * nrot times; four heads are in flight per step.
   const int vec_per_head = HN >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_vec;
-       i += (long long)gridDim.x * blockDim.x) {
-    int v = (int)(i % vec_per_head);
-    long long r = i / vec_per_head;
-    int slot = (int)(r % nrot);
-    r /= nrot;
-    int g = (int)(r % G);
-    long long t = r / G;
-    int b = (int)(t % B);
-    int s = (int)(t / B);
-    long long pos = pos_ids ? pos_ids[(long long)b * S + s] : (long long)(s + pos_offset);
-    if (pos >= max_pos) pos = max_pos - 1;
-    bf16x8* p = reinterpret_cast<bf16x8*>(x + (((t * G + g) * nslot + slot) * (long long)HN)) + v;
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= total_vec) return;
+  const int v = (int)(i % vec_per_head);
+  const long long t = i / vec_per_head;
+  const int b = (int)(t % B);
+  const int s = (int)(t / B);
+  long long pos = pos_ids ? pos_ids[(long long)b * S + s] : (long long)(s + pos_offset);
+  if (pos >= max_pos) pos = max_pos - 1;
+  const float2* cs = table + pos * (HN >> 1) + v * 4;
+  float cx[4], sn[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float2 c = cs[k];
+    cx[k] = c.x;
+    sn[k] = c.y * sign;
+  }
+  bf16x8* base = reinterpret_cast<bf16x8*>(x + t * (long long)G * nslot * HN) + v;
+  const int heads = G * nrot;
+  auto head_ptr = [&](int h) {
+    const int g = h / nrot, slot = h - g * nrot;
+    return base + (long long)(g * nslot + slot) * vec_per_head;
+  };
+  auto rotate = [&](bf16x8 in) {
     float f[8], o[8];
-    unpack8(*p, f);
-    const float2* cs = table + pos * (HN >> 1) + v * 4;
+    unpack8(in, f);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      float2 c = cs[k];
-      float sn = c.y * sign;
-      o[2 * k] = f[2 * k] * c.x - f[2 * k + 1] * sn;
-      o[2 * k + 1] = f[2 * k] * sn + f[2 * k + 1] * c.x;
+      o[2 * k] = f[2 * k] * cx[k] - f[2 * k + 1] * sn[k];
+      o[2 * k + 1] = f[2 * k] * sn[k] + f[2 * k + 1] * cx[k];
     }
-    *p = pack8(o);
+    return pack8(o);
+  };
+  int h = 0;
+  for (; h + 4 <= heads; h += 4) {
+    bf16x8* p[4];
+    bf16x8 in[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      p[u] = head_ptr(h + u);
+      in[u] = *p[u];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) *p[u] = rotate(in[u]);
+  }
+  for (; h < heads; ++h) {
+    bf16x8* p = head_ptr(h);
+    *p = rotate(*p);
   }
 }
 
@@ -85,47 +111,73 @@ __device__ __forceinline__ float glu_act_grad(float g) {
   return sg * (1.f + g * (1.f - sg));
 }
 
-// in: [M, 2F] (x1 | x2), out: [M, F] = x1 * act(x2)
+// in: [M, 2F] (x1 | x2), out: [M, F] = x1 * act(x2).
+// Grid (ceil(F/8 / 128), ceil(M / kGluRows)): a thread owns one 16-byte column of kGluRows rows,
+// issues all its loads first, and never divides.
+constexpr int kGluRows = 4;
 template <int kKind>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 glu_fwd_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int F,
-               long long total_vec) {
+               long long M) {
   const int vpr = F >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_vec;
-       i += (long long)gridDim.x * blockDim.x) {
-    long long row = i / vpr;
-    int v = (int)(i % vpr);
-    const bf16x8* r = reinterpret_cast<const bf16x8*>(in + row * 2 * F);
-    float a[8], g[8], o[8];
-    unpack8(r[v], a);
-    unpack8(r[v + vpr], g);
+  const int v = blockIdx.x * 128 + threadIdx.x;
+  if (v >= vpr) return;
+  const long long row0 = (long long)blockIdx.y * kGluRows;
+  bf16x8 A[kGluRows], Gt[kGluRows];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = a[k] * glu_act<kKind>(g[k]);
-    reinterpret_cast<bf16x8*>(out + row * F)[v] = pack8(o);
+  for (int u = 0; u < kGluRows; ++u) {
+    if (row0 + u < M) {
+      const bf16x8* r = reinterpret_cast<const bf16x8*>(in + (row0 + u) * 2 * F);
+      A[u] = r[v];
+      Gt[u] = r[v + vpr];
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < kGluRows; ++u) {
+    if (row0 + u < M) {
+      float a[8], g[8], o[8];
+      unpack8(A[u], a);
+      unpack8(Gt[u], g);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = a[k] * glu_act<kKind>(g[k]);
+      reinterpret_cast<bf16x8*>(out + (row0 + u) * F)[v] = pack8(o);
+    }
   }
 }
 template <int kKind>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 glu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ in,
-               __nv_bfloat16* __restrict__ din, int F, long long total_vec) {
+               __nv_bfloat16* __restrict__ din, int F, long long M) {
   const int vpr = F >> 3;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_vec;
-       i += (long long)gridDim.x * blockDim.x) {
-    long long row = i / vpr;
-    int v = (int)(i % vpr);
-    const bf16x8* r = reinterpret_cast<const bf16x8*>(in + row * 2 * F);
-    float a[8], g[8], d[8], da[8], dg[8];
-    unpack8(r[v], a);
-    unpack8(r[v + vpr], g);
-    unpack8(reinterpret_cast<const bf16x8*>(dy + row * F)[v], d);
+  const int v = blockIdx.x * 128 + threadIdx.x;
+  if (v >= vpr) return;
+  const long long row0 = (long long)blockIdx.y * kGluRows;
+  bf16x8 A[kGluRows], Gt[kGluRows], D[kGluRows];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      da[k] = d[k] * glu_act<kKind>(g[k]);
-      dg[k] = d[k] * a[k] * glu_act_grad<kKind>(g[k]);
+  for (int u = 0; u < kGluRows; ++u) {
+    if (row0 + u < M) {
+      const bf16x8* r = reinterpret_cast<const bf16x8*>(in + (row0 + u) * 2 * F);
+      A[u] = r[v];
+      Gt[u] = r[v + vpr];
+      D[u] = reinterpret_cast<const bf16x8*>(dy + (row0 + u) * F)[v];
     }
-    bf16x8* w = reinterpret_cast<bf16x8*>(din + row * 2 * F);
-    w[v] = pack8(da);
-    w[v + vpr] = pack8(dg);
+  }
+#pragma unroll
+  for (int u = 0; u < kGluRows; ++u) {
+    if (row0 + u < M) {
+      float a[8], g[8], d[8], da[8], dg[8];
+      unpack8(A[u], a);
+      unpack8(Gt[u], g);
+      unpack8(D[u], d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        da[k] = d[k] * glu_act<kKind>(g[k]);
+        dg[k] = d[k] * a[k] * glu_act_grad<kKind>(g[k]);
+      }
+      bf16x8* w = reinterpret_cast<bf16x8*>(din + (row0 + u) * 2 * F);
+      w[v] = pack8(da);
+      w[v + vpr] = pack8(dg);
+    }
   }
 }
 
@@ -269,9 +321,10 @@ B200_API int b200_rope(void* x, const float* cos_sin, const long long* pos_ids, 
                        int nslot, int nrot, int HN, int pos_offset, int max_pos, int inverse,
                        cudaStream_t stream) {
   if (HN % 8 || nrot > nslot || nrot <= 0) return B200_ERR_UNSUPPORTED;
-  long long total = (long long)S * B * G * nrot * (HN >> 3);
-  if (total == 0) return 0;
-  rope_kernel<<<ew_grid(total), 256, 0, stream>>>((__nv_bfloat16*)x, (const float2*)cos_sin,
+  long long total = (long long)S * B * (HN >> 3);      // one thread per (token, 16-byte column)
+  if (total == 0 || G == 0) return 0;
+  if ((total + 127) / 128 > 0x7fffffffLL) return B200_ERR_TOO_LARGE;
+  rope_kernel<<<(unsigned)((total + 127) / 128), 128, 0, stream>>>((__nv_bfloat16*)x, (const float2*)cos_sin,
                                                   pos_ids, S, B, G, nslot, nrot, HN, pos_offset,
                                                   max_pos, inverse ? -1.f : 1.f, total);
   B200_CHECK_LAUNCH();
@@ -283,14 +336,21 @@ B200_API int b200_glu_fwd(const void* in, void* out, long long M, int F, int kin
   if (F % 8 || kind < 0 || kind > 3) return B200_ERR_UNSUPPORTED;
   long long total = M * (F >> 3);
   if (total == 0) return 0;
-  int g = ew_grid(total);
   const __nv_bfloat16* i = (const __nv_bfloat16*)in;
   __nv_bfloat16* o = (__nv_bfloat16*)out;
-  switch (kind) {
-    case kLiGLU: glu_fwd_kernel<kLiGLU><<<g, 256, 0, stream>>>(i, o, F, total); break;
-    case kGEGLU: glu_fwd_kernel<kGEGLU><<<g, 256, 0, stream>>>(i, o, F, total); break;
-    case kReGLU: glu_fwd_kernel<kReGLU><<<g, 256, 0, stream>>>(i, o, F, total); break;
-    default: glu_fwd_kernel<kSwiGLU><<<g, 256, 0, stream>>>(i, o, F, total); break;
+  // gridDim.y is limited to 65535: very tall inputs go in slabs
+  const long long slab = 65535LL * kGluRows;
+  for (long long m0 = 0; m0 < M; m0 += slab) {
+    const long long m = M - m0 < slab ? M - m0 : slab;
+    dim3 g((unsigned)(((F >> 3) + 127) / 128), (unsigned)((m + kGluRows - 1) / kGluRows));
+    const __nv_bfloat16* ii = i + m0 * 2 * F;
+    __nv_bfloat16* oo = o + m0 * F;
+    switch (kind) {
+      case kLiGLU: glu_fwd_kernel<kLiGLU><<<g, 128, 0, stream>>>(ii, oo, F, m); break;
+      case kGEGLU: glu_fwd_kernel<kGEGLU><<<g, 128, 0, stream>>>(ii, oo, F, m); break;
+      case kReGLU: glu_fwd_kernel<kReGLU><<<g, 128, 0, stream>>>(ii, oo, F, m); break;
+      default: glu_fwd_kernel<kSwiGLU><<<g, 128, 0, stream>>>(ii, oo, F, m); break;
+    }
   }
   B200_CHECK_LAUNCH();
   return 0;
@@ -301,15 +361,22 @@ B200_API int b200_glu_bwd(const void* dy, const void* in, void* din, long long M
   if (F % 8 || kind < 0 || kind > 3) return B200_ERR_UNSUPPORTED;
   long long total = M * (F >> 3);
   if (total == 0) return 0;
-  int g = ew_grid(total);
   const __nv_bfloat16* d = (const __nv_bfloat16*)dy;
   const __nv_bfloat16* i = (const __nv_bfloat16*)in;
   __nv_bfloat16* o = (__nv_bfloat16*)din;
-  switch (kind) {
-    case kLiGLU: glu_bwd_kernel<kLiGLU><<<g, 256, 0, stream>>>(d, i, o, F, total); break;
-    case kGEGLU: glu_bwd_kernel<kGEGLU><<<g, 256, 0, stream>>>(d, i, o, F, total); break;
-    case kReGLU: glu_bwd_kernel<kReGLU><<<g, 256, 0, stream>>>(d, i, o, F, total); break;
-    default: glu_bwd_kernel<kSwiGLU><<<g, 256, 0, stream>>>(d, i, o, F, total); break;
+  const long long slab = 65535LL * kGluRows;
+  for (long long m0 = 0; m0 < M; m0 += slab) {
+    const long long m = M - m0 < slab ? M - m0 : slab;
+    dim3 g((unsigned)(((F >> 3) + 127) / 128), (unsigned)((m + kGluRows - 1) / kGluRows));
+    const __nv_bfloat16* dd = d + m0 * F;
+    const __nv_bfloat16* ii = i + m0 * 2 * F;
+    __nv_bfloat16* oo = o + m0 * 2 * F;
+    switch (kind) {
+      case kLiGLU: glu_bwd_kernel<kLiGLU><<<g, 128, 0, stream>>>(dd, ii, oo, F, m); break;
+      case kGEGLU: glu_bwd_kernel<kGEGLU><<<g, 128, 0, stream>>>(dd, ii, oo, F, m); break;
+      case kReGLU: glu_bwd_kernel<kReGLU><<<g, 128, 0, stream>>>(dd, ii, oo, F, m); break;
+      default: glu_bwd_kernel<kSwiGLU><<<g, 128, 0, stream>>>(dd, ii, oo, F, m); break;
+    }
   }
   B200_CHECK_LAUNCH();
   return 0;

@@ -202,6 +202,23 @@ def bench_elementwise():
     by = 3.0 * M * F * 2
     report(kernel="swiglu_fwd", M=M, F=F, ms_own=t_own, ms_eager=t_lib, gbs_own=by / t_own / 1e6,
            frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+    dy = torch.randn(M, F, device="cuda").bfloat16()
+    dx = torch.empty_like(x)
+    t_own = timeit(lambda: L.call("b200_glu_bwd", dy.data_ptr(), x.data_ptr(), dx.data_ptr(), M, F, 3,
+                                  L.stream_ptr()))
+    by = 5.0 * M * F * 2
+    report(kernel="swiglu_bwd", M=M, F=F, ms_own=t_own, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+    S, G, NS, HN = 4096, 32, 3, 128
+    qkv = torch.randn(S, 1, G, NS, HN, device="cuda").bfloat16()
+    inv = 1.0 / (10000 ** (torch.arange(0, HN, 2, device="cuda").float() / HN))
+    ang = torch.outer(torch.arange(S, device="cuda").float(), inv)
+    table = torch.stack([ang.cos(), ang.sin()], -1).contiguous()
+    t_own = timeit(lambda: L.call("b200_rope", qkv.data_ptr(), table.data_ptr(), None, S, 1, G, NS, NS - 1, HN,
+                                  0, S, 0, L.stream_ptr()))
+    by = 2.0 * S * G * (NS - 1) * HN * 2
+    report(kernel="rope_fused_qkv", S=S, G=G, HN=HN, ms_own=t_own, gbs_own=by / t_own / 1e6,
+           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
     T, V = 4096, 32000
     logits = torch.randn(T, V, device="cuda").bfloat16()
     labels = torch.randint(0, V, (T,), device="cuda")

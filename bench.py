@@ -50,7 +50,7 @@ def build_arg_list(a, tp, dp):
     gbs = a.micro_batch * a.num_microbatches * dp
     argv = [
         "--b200_kernels", getattr(a, 'kernels', 'auto'), "--b200_fused_comm", getattr(a, 'fused_comm', 'auto'),
-        "--b200_fused_dp", getattr(a, 'fused_dp', 'auto'),
+        "--b200_fused_dp", getattr(a, 'fused_dp', 'auto'), "--ddp_bucket_mb", str(getattr(a, 'bucket_mb', 256)),
         "--model_name", "llama2", "--num_layers", str(L), "--hidden_size", str(h),
         "--num_attention_heads", str(nh), "--num_attention_heads_kv", str(nkv),
         "--ffn_hidden_size", str(ffn), "--seq_length", str(a.seq), "--max_position_embeddings", str(a.seq),
@@ -302,6 +302,7 @@ def main():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--model", default="llama2-7b", choices=list(MODELS))
+    p.add_argument("--bucket_mb", type=float, default=256, help="A/B only: gradient bucket size")
     p.add_argument("--tp", type=int, default=0, help="A/B only: override the tensor-parallel size (default: 2 for N>=2)")
     p.add_argument("--seq", type=int, default=4096)
     p.add_argument("--micro_batch", type=int, default=1)

@@ -127,10 +127,15 @@ class DistributedDataParallel(DistributedDataParallelBase):
         self.layout = {}        # dtype -> [(param, start, end, key)] in buffer order
         self.group_ranges = {}  # dtype -> {key: (start, end)}
         cursor = {dt: 0 for dt in sizes}
+        self._bucket_cuts = {dt: set() for dt in sizes}
+        import os
+        lanes_on = fused_dp and os.environ.get("B200_DP_LANES", "1") != "0"
         for key in keys:
             members = [(i, p) for k, i, p in keyed if k == key]
-            for i, p in reversed(members):
+            for i, p, cut in self._buffer_order(list(reversed(members)), buf_dtype, dp if lanes_on else 1):
                 dt = buf_dtype(p)
+                if cut:
+                    self._bucket_cuts[dt].add((cursor[dt] + 7) // 8 * 8)
                 start = cursor[dt]
                 # keep every parameter 16-byte aligned in the bf16 mirror of this index space
                 start = (start + 7) // 8 * 8
@@ -162,6 +167,30 @@ class DistributedDataParallel(DistributedDataParallelBase):
             acc.register_hook(self._make_param_hook(p))
             self.grad_accs.append(acc)
 
+    def _buffer_order(self, produced, buf_dtype, lanes):
+        """(index, param, starts_a_bucket) in buffer order. ``produced`` is the order in which
+        backward finishes the gradients. With ``lanes`` > 1 (fused data-parallel reduction, where a
+        rank reduces the buckets that fall into ITS contiguous 1/dp of the buffer) bucket-sized
+        runs of parameters are dealt round-robin to ``lanes`` regions laid out one after the
+        other, so consecutive buckets of the backward pass belong to different owners and no
+        rank ends up with all of its reduction work at the very end of the step."""
+        if lanes <= 1:
+            return [(i, p, False) for i, p in produced]
+        runs, cur, size = [], [], 0
+        for i, p in produced:
+            cur.append((i, p))
+            size += p.data.nelement() * torch.empty((), dtype=buf_dtype(p)).element_size()
+            if size >= self.bucket_bytes:
+                runs.append(cur)
+                cur, size = [], 0
+        if cur:
+            runs.append(cur)
+        out = []
+        for lane in range(lanes):
+            for run in runs[lane::lanes]:
+                out += [(i, p, j == 0) for j, (i, p) in enumerate(run)]
+        return out
+
     def _make_param_hook(self, param):
         def hook(*unused):
             if param.grad is not None:
@@ -184,7 +213,10 @@ class DistributedDataParallel(DistributedDataParallelBase):
             esz = self._grad_buffers[dt].data.element_size()
             cur = None
             first = len(self._buckets)
+            cuts = self._bucket_cuts.get(dt, ())
             for p, start, end, _ in items:
+                if start in cuts:
+                    cur = None
                 if cur is None:
                     cur = _Bucket(dt, start, len(self._buckets) - first)
                     self._buckets.append(cur)

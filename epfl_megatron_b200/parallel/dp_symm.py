@@ -90,6 +90,9 @@ class DPWorkspace:
         self.epoch = 0          # one per training step (bucket flags)
         self.param_epoch = 0    # one per successful optimizer step
         self.side = torch.cuda.Stream(device=self.device)
+        # "my bucket is final" stores go out on their own stream, which never waits for a peer, so
+        # the order in which ranks get to their waits cannot matter
+        self.sig = torch.cuda.Stream(device=self.device)
         self.blocks_overlap = int(os.environ.get("B200_DP_BLOCKS", "96"))
         self.blocks_exposed = 148 * 4
         self.allow_overlap = os.environ.get("B200_DP_NO_OVERLAP", "0") != "1"
@@ -109,14 +112,16 @@ class DPWorkspace:
         main = torch.cuda.current_stream()
         overlapped = overlapped and self.allow_overlap
         if overlapped:
+            self.sig.wait_stream(main)
             self.side.wait_stream(main)
-            stream = self.side
+            stream, sig = self.side, self.sig
             self._pending = True
         else:
             if self._pending:
                 main.wait_stream(self.side)
+                main.wait_stream(self.sig)
                 self._pending = False
-            stream = main
+            stream = sig = main
         st = stream.cuda_stream
         dp, me = self.dp, self.rank
         word = index * dp
@@ -126,7 +131,7 @@ class DPWorkspace:
             if r != me:
                 addrs[n] = self.peer_flags[r] + 4 * (word + me)
                 n += 1
-        L.call("b200_symm_signal", addrs, n, self.epoch & 0xFFFFFFFF, st)
+        L.call("b200_symm_signal", addrs, n, self.epoch & 0xFFFFFFFF, sig.cuda_stream)
         lo, hi = max(start, self.shard_lo), min(end, self.shard_hi)
         if lo < hi:
             grads = (C.c_void_p * 8)()
@@ -149,6 +154,7 @@ class DPWorkspace:
     def finish(self):
         if self._pending:
             torch.cuda.current_stream().wait_stream(self.side)
+            torch.cuda.current_stream().wait_stream(self.sig)
             self._pending = False
 
     # ---- parameters ------------------------------------------------------------------------

@@ -1,0 +1,4 @@
+set -x
+B="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1"
+timeout 600 $B --master-port 29511 bench.py --gpus 8 --steps 6 --warmup 3 > gpurun_out/bench_n8_fused_lanes.log 2>&1; echo "n8 fused lanes rc=$?"; tail -1 gpurun_out/bench_n8_fused_lanes.log | grep -o '"ms_per_step": [0-9.]*'
+timeout 600 $B --master-port 29514 bench.py --gpus 8 --steps 6 --warmup 3 --fused_dp off > gpurun_out/bench_n8_nccl2.log 2>&1; echo "n8 nccl rc=$?"; tail -1 gpurun_out/bench_n8_nccl2.log | grep -o '"ms_per_step": [0-9.]*'

@@ -31,12 +31,14 @@ MODELS = {
     "llama2-13b": (40, 5120, 40, 40, 13824, 32000),
     "llama2-70b": (80, 8192, 64, 8, 28672, 32000),
     "tiny": (2, 256, 8, 2, 688, 32000),
+    # Falcon: LayerNorm, GeLU MLP of 4h, parallel attention / MLP block, tied embeddings
+    "falcon-40b": (60, 8192, 128, 8, 32768, 65024),
 }
 
 
-def parallel_layout(n_gpus, model, tp_override=0):
+def parallel_layout(n_gpus, model, tp_override=0, pp=1):
     if tp_override:
-        return tp_override, n_gpus // tp_override
+        return tp_override, n_gpus // (tp_override * pp)
     if model == "tiny":
         return (1, n_gpus) if n_gpus < 2 else (2, n_gpus // 2)
     tp = 1 if n_gpus == 1 else 2
@@ -51,17 +53,19 @@ def build_arg_list(a, tp, dp):
     argv = [
         "--b200_kernels", getattr(a, 'kernels', 'auto'), "--b200_fused_comm", getattr(a, 'fused_comm', 'auto'),
         "--b200_fused_dp", getattr(a, 'fused_dp', 'auto'), "--ddp_bucket_mb", str(getattr(a, 'bucket_mb', 256)),
-        "--model_name", "llama2", "--num_layers", str(L), "--hidden_size", str(h),
+        "--model_name", "falcon" if a.model.startswith("falcon") else "llama2",
+        "--num_layers", str(L), "--hidden_size", str(h),
         "--num_attention_heads", str(nh), "--num_attention_heads_kv", str(nkv),
         "--ffn_hidden_size", str(ffn), "--seq_length", str(a.seq), "--max_position_embeddings", str(a.seq),
         "--micro_batch_size", str(a.micro_batch), "--global_batch_size", str(gbs),
         "--train_iters", str(a.steps * 2 + a.warmup + 8), "--lr", "1e-5", "--min_lr", "1e-6",
         "--lr_decay_style", "cosine", "--lr_warmup_iters", "1", "--weight_decay", "0.1",
         "--adam_beta2", "0.95", "--clip_grad", "1.0",
-        "--use_rms_norm", "--glu_activation", "swiglu", "--no_tie_embed_logits",
+        *(["--parallel_attn", "--parallel_layernorm"] if a.model.startswith("falcon") else
+          ["--use_rms_norm", "--glu_activation", "swiglu", "--no_tie_embed_logits"]),
         "--position_embedding_type", "rotary", "--use_flash_attn", "--no_bias_gelu_fusion",
         "--hidden_dropout", "0.0", "--attention_dropout", "0.0", "--bf16",
-        "--tensor_model_parallel_size", str(tp), "--pipeline_model_parallel_size", "1",
+        "--tensor_model_parallel_size", str(tp), "--pipeline_model_parallel_size", str(getattr(a, 'pp', 1)),
         "--use_distributed_optimizer", "--tokenizer_type", "NullTokenizer",
         "--make_vocab_size_divisible_by", "128", "--synthetic_data", "--num_workers", "0",
         "--log_interval", "1000000", "--eval_iters", "0", "--eval_interval", "1000000",
@@ -70,6 +74,8 @@ def build_arg_list(a, tp, dp):
         argv.append("--sequence_parallel")
     if a.recompute:
         argv += ["--recompute_granularity", "full", "--recompute_method", "uniform"]
+    if getattr(a, 'vpp_layers', 0):
+        argv += ["--num_layers_per_virtual_pipeline_stage", str(a.vpp_layers)]
     return argv, gbs
 
 
@@ -122,7 +128,7 @@ def run_ours(a):
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
-    tp, dp = parallel_layout(a.gpus, a.model, getattr(a, 'tp', 0))
+    tp, dp = parallel_layout(a.gpus, a.model, getattr(a, 'tp', 0), getattr(a, 'pp', 1))
     argv, gbs = build_arg_list(a, tp, dp)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29400")
@@ -152,6 +158,8 @@ def run_ours(a):
             i += 1
 
     it = batches() if mpu.get_tensor_model_parallel_rank() == 0 else None
+    if args.virtual_pipeline_model_parallel_size is not None:
+        it = [batches() if mpu.get_tensor_model_parallel_rank() == 0 else None for _ in range(len(model))]
     h2d_bytes = n_mb * pool[0].numel() * pool[0].element_size()
 
     def step():
@@ -246,7 +254,8 @@ def run_ours(a):
         sys.stdout = real_stdout
     if rank == 0:
         out = {
-            "metric": "Llama-2 7B bf16 training throughput (tokens/s, whole job, max over ranks)",
+            "metric": ("Llama-2 7B" if a.model == "llama2-7b" else a.model) +
+                      " bf16 training throughput (tokens/s, whole job, max over ranks)",
             "value": value, "unit": "tokens/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": value / 7100.0 if a.model == "llama2-7b" else None,
@@ -254,7 +263,9 @@ def run_ours(a):
             "impl": "ours",
             "config": {"model": a.model, "global_batch": args.global_batch_size, "seq_len": args.seq_length,
                        "micro_batch": args.micro_batch_size, "num_microbatches": n_mb,
-                       "parallelism": f"tp{tp}" + (f"dp{dp}" if dp > 1 else ""),
+                       "parallelism": f"tp{tp}" + (f"pp{a.pp}" if a.pp > 1 else "") + (f"dp{dp}" if dp > 1 else "")
+                                      + (f" interleaved x{len(model)}" if len(model) > 1 else "")
+                                      + (" full-recompute" if a.recompute else ""),
                        "sequence_parallel": bool(args.sequence_parallel), "distributed_optimizer": True,
                        "l2_policy": "inputs larger than L2 (13.5 GB of weights streamed every step)",
                        "baseline_note": "vs_baseline divides by 7.1k tokens/s derived from the reference's "
@@ -285,7 +296,7 @@ def run_reference(a):
                 print(json.dumps({"impl": "reference", "unavailable":
                                   "reference sources not present under baseline/_ref: " + r.stderr[-200:]}))
             return 0
-    tp, dp = parallel_layout(a.gpus, a.model, getattr(a, 'tp', 0))
+    tp, dp = parallel_layout(a.gpus, a.model, getattr(a, 'tp', 0), getattr(a, 'pp', 1))
     cmd = [sys.executable, script, "--model", a.model, "--gpus", str(a.gpus), "--steps", str(a.steps),
            "--warmup", str(a.warmup), "--seq", str(a.seq), "--micro_batch", str(a.micro_batch),
            "--num_microbatches", str(a.num_microbatches), "--tp", str(tp), "--dp", str(dp),
@@ -303,6 +314,8 @@ def main():
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--model", default="llama2-7b", choices=list(MODELS))
     p.add_argument("--bucket_mb", type=float, default=256, help="A/B only: gradient bucket size")
+    p.add_argument("--pp", type=int, default=1, help="other BASELINE configs only: pipeline-parallel size")
+    p.add_argument("--vpp_layers", type=int, default=0, help="layers per virtual pipeline stage (interleaved 1F1B)")
     p.add_argument("--tp", type=int, default=0, help="A/B only: override the tensor-parallel size (default: 2 for N>=2)")
     p.add_argument("--seq", type=int, default=4096)
     p.add_argument("--micro_batch", type=int, default=1)

@@ -155,6 +155,27 @@ int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int
                              const void* B, void* out, int M, int N, int K, int b_mn_major, long long lda,
                              long long ldb, unsigned rs_target, cudaStream_t stream);
 
+/* ---- data-parallel reduce-scatter / Adam with parameter all-gather over peer memory (csrc/dp_comm.cu) --
+ * Replaces megatron/optimizer/distrib_optimizer.py:553-567 and :592-608. Buffers come from b200_symm_alloc and
+ * are mapped by the peers (b200_symm_export / b200_symm_import).
+ * b200_dp_reduce: in place, grads[rank][i] = scale * sum_r grads[r][i] for n floats (n % 4 == 0); grads[r] is
+ *   rank r's address of the slice (peer-mapped or local staging); waits until the local flag words ready[r]
+ *   (r != rank) have reached `epoch`; `blocks` = grid size.
+ * b200_adam_step_push: b200_adam_step on n elements (n % 8 == 0) whose bf16 result is stored to n_dst
+ *   parameter buffers (own + peers).
+ * b200_dp_wait: bounded stream-ordered wait for flags[i] >= value, i < n, i != skip; a time-out is recorded
+ *   (site, value seen, target, index, block) and returned once by b200_dp_debug_read (all zero: none).
+ * b200_copy_async: copy-engine transfer, src may be peer-mapped. */
+int b200_dp_reduce(const void* const* grads, int dp, int rank, long long n, float scale, const unsigned* ready,
+                   unsigned epoch, int blocks, cudaStream_t stream);
+int b200_adam_step_push(float* p, const float* g, float* m, float* v, void* const* p16_dst, int n_dst,
+                        long long n, float lr, float beta1, float beta2, float eps, float wd, int step,
+                        int adamw, int bias_correction, const float* coef, const float* skip,
+                        cudaStream_t stream);
+int b200_dp_wait(const unsigned* flags, int n, int skip, unsigned value, unsigned site, cudaStream_t stream);
+int b200_copy_async(void* dst, const void* src, long long bytes, cudaStream_t stream);
+int b200_dp_debug_read(unsigned* out8);
+
 /* ---- tcgen05 attention (csrc/attn_fwd_tcgen05.cu) --------------------------------------- */
 /* Causal / full GQA attention forward reading q, k, v through arbitrary element strides
  * (the fused QKV projection layout [s, b, g, q_per_g+2, hn] needs no copies). hn must be 128.

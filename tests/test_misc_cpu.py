@@ -63,3 +63,23 @@ def test_distrib_optimizer_module_path():
     from megatron.optimizer.distrib_optimizer import DistributedOptimizer, Range
     r = Range(8, 24).normalize(100)
     assert (r.start, r.end, r.size) == (100, 116, 16) and DistributedOptimizer.__name__ == "DistributedOptimizer"
+
+
+def test_fused_dp_buffer_order_rotates_bucket_owners():
+    """Bucket-sized runs of parameters (in gradient production order) are dealt round-robin over the
+    dp regions of the buffer, each run starting a bucket (models/distributed.py::_buffer_order)."""
+    import types
+
+    import torch
+    from epfl_megatron_b200.models.distributed import DistributedDataParallel as DDP
+
+    params = [torch.nn.Parameter(torch.zeros(n)) for n in (100, 30, 80, 60, 10, 120, 40, 90, 70)]
+    produced = list(enumerate(params))
+    fake = types.SimpleNamespace(bucket_bytes=100 * 4)
+    flat = DDP._buffer_order(fake, produced, lambda p: torch.float32, 1)
+    assert [i for i, _, _ in flat] == list(range(9)) and not any(c for _, _, c in flat)
+    out = DDP._buffer_order(fake, produced, lambda p: torch.float32, 2)
+    # runs by >= 400 bytes: [0] [1,2] [3,4,5] [6,7] [8]; lane 0 takes runs 0,2,4, lane 1 runs 1,3
+    assert [i for i, _, _ in out] == [0, 3, 4, 5, 8, 1, 2, 6, 7]
+    assert [i for i, _, c in out if c] == [0, 3, 8, 1, 6]
+    assert sorted(i for i, _, _ in out) == list(range(9))

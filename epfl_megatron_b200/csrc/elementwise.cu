@@ -100,14 +100,14 @@ __device__ __forceinline__ float glu_act(float g) {
   if (kKind == kLiGLU) return g;
   if (kKind == kGEGLU) return gelu_erf(g);
   if (kKind == kReGLU) return fmaxf(g, 0.f);
-  return g / (1.f + __expf(-g));
+  return __fdividef(g, 1.f + __expf(-g));
 }
 template <int kKind>
 __device__ __forceinline__ float glu_act_grad(float g) {
   if (kKind == kLiGLU) return 1.f;
   if (kKind == kGEGLU) return gelu_erf_grad(g);
   if (kKind == kReGLU) return g > 0.f ? 1.f : 0.f;
-  float sg = 1.f / (1.f + __expf(-g));
+  float sg = __fdividef(1.f, 1.f + __expf(-g));
   return sg * (1.f + g * (1.f - sg));
 }
 

@@ -223,7 +223,9 @@ _GROUPS = {
         ("--bert_binary_head", dict(action=T, default=True)),
         ("--log_learning_rate_to_tensorboard", dict(type=bool, default=True)),
         ("--log_loss_scale_to_tensorboard", dict(type=bool, default=True)),
-        ("--fault_inject", dict(type=str)),               # test hook, see utils/fault.py
+        ("--fault_inject", dict(type=str)),
+        ("--nvtx_ranges", dict(action=T)),                 # NVTX range per timer interval (all levels)
+        ("--check_dp_consistency_interval", dict(type=int, default=0)),   # debug: checksum params across DP               # test hook, see utils/fault.py
     ],
 }
 

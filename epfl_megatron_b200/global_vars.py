@@ -85,6 +85,10 @@ def set_global_variables(args, build_tokenizer_flag=True):
         _build_tokenizer(args)
     _set_tensorboard_writer(args)
     _set_adlr_autoresume(args)
+    if getattr(args, "nvtx_ranges", False):
+        from .timers import set_nvtx_ranges
+        set_nvtx_ranges(True)
+        args.timing_log_level = 2       # every phase gets a (real) timer, hence a range
     _TIMERS = Timers(args.timing_log_level, args.timing_log_option)
     if args.exit_signal_handler:
         _set_signal_handler()

@@ -304,6 +304,28 @@ class FlatOptimizer(MegatronOptimizer):
                 all_gather_into(ch.param, ch.param[ch.shard_lo:ch.shard_hi], grp)
         timers("params-all-gather").stop()
 
+    def check_dp_consistency(self):
+        """Debug aid for the in-kernel collectives: after a step every
+        data-parallel replica must hold bit-identical parameters. Compares a 64-bit checksum of each
+        parameter buffer across the data-parallel group and raises on the first mismatch. Syncs."""
+        if not dist.is_initialized() or mpu.get_data_parallel_world_size() == 1:
+            return
+        grp = mpu.get_data_parallel_group()
+        for i, ch in enumerate(self.chunks):
+            words = ch.param.view(torch.int16 if ch.param.element_size() == 2 else torch.int32)
+            # position-weighted so that swapped shards do not cancel
+            n = words.numel()
+            w = (torch.arange(n, device=words.device, dtype=torch.int64) % 8191) + 1
+            cs = (words.to(torch.int64) * w).sum().view(1)
+            lo, hi = cs.clone(), cs.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=grp)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=grp)
+            if int(lo) != int(hi):
+                raise RuntimeError(f"data-parallel replicas diverged: parameter buffer {i} checksum {int(cs)} on "
+                                   f"dp rank {mpu.get_data_parallel_rank()}, group min {int(lo)} max {int(hi)}")
+            if ch.ws is not None:
+                ch.ws.check()
+
     # ------------------------------------------------------------------ step
     def _grad_sumsq(self):
         """out[0] = sum of squares of the locally owned, non-duplicated gradients; out[1] =

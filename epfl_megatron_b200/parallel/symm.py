@@ -17,6 +17,7 @@ Ordering rules the callers rely on (all ranks make the same calls in the same or
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -81,6 +82,14 @@ class TPWorkspace:
         self.rs_calls = 0
         self._descs = [self._make_desc(i) for i in range(2)]
         self._flags = _wrap(self.base, self.flag_bytes, self.device).view(torch.int32)
+        # Debug modes. B200_COMM_POISON=1: after every reduce-scatter the
+        # partial-sum slots it consumed are overwritten with bf16 NaNs, so a later call that reads a
+        # slot before its producer wrote it shows up as NaNs instead of plausible stale numbers.
+        # B200_COMM_VERIFY=1: every fused call is checked against NCCL + a plain matmul (slow).
+        self.poison = os.environ.get("B200_COMM_POISON", "0") == "1"
+        self.verify = os.environ.get("B200_COMM_VERIFY", "0") == "1"
+        self._parts_view = [
+            _wrap(self._parts(self.rank, s_), self.parts_bytes, self.device).view(torch.int16) for s_ in range(2)]
 
     # ---- addresses -------------------------------------------------------------------------
     def _stage(self, r, i):
@@ -128,6 +137,15 @@ class TPWorkspace:
         out = torch.empty(M, N, device=self.device, dtype=torch.bfloat16)
         L.call("b200_gemm_allgather", C.byref(self._descs[stage]), gathered.data_ptr(), weight.data_ptr(),
                out.data_ptr(), M, N, K, int(b_mn_major), weight.stride(0), N, e, st)
+        if self.verify:
+            ref = torch.empty_like(gathered)
+            dist.all_gather_into_tensor(ref, x_shard, group=self.group)
+            if not torch.equal(ref, gathered):
+                raise RuntimeError(f"fused all-gather (call {e}, rank {self.rank}): gathered rows differ from NCCL")
+            want = ref.float() @ (weight.float() if b_mn_major else weight.float().t())
+            err = (out.float() - want).abs().max().item()
+            if not err <= 2e-2 * max(want.abs().max().item(), 1.0):
+                raise RuntimeError(f"fused all-gather GEMM (call {e}, rank {self.rank}): max abs error {err}")
         return out, gathered
 
     # ---- GEMM -> reduce-scatter ------------------------------------------------------------
@@ -149,6 +167,16 @@ class TPWorkspace:
         L.call("b200_gemm_reduce_scatter", C.byref(self._descs[0]), parts, s, a.data_ptr(), weight.data_ptr(),
                out.data_ptr(), M, N, K, int(b_mn_major), a.stride(0), weight.stride(0),
                arrivals, L.stream_ptr())
+        if self.poison:
+            self._parts_view[s].fill_(-1)       # 0xFFFF = bf16 NaN; consumed slots of this call only
+        if self.verify:
+            full = a.float() @ (weight.float() if b_mn_major else weight.float().t())
+            want = torch.empty(rpc, N, device=self.device, dtype=torch.float32)
+            dist.reduce_scatter_tensor(want, full, group=self.group)
+            err = (out.float() - want).abs().max().item()
+            if not err <= 3e-2 * max(want.abs().max().item(), 1.0):
+                raise RuntimeError(f"fused GEMM reduce-scatter (call {self.rs_calls}, rank {self.rank}): "
+                                   f"max abs error {err}")
         return out
 
     def check(self):

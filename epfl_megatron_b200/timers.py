@@ -39,6 +39,16 @@ class DummyTimer(_Base):
         raise Exception("dummy timer should not be used to calculate elapsed time")
 
 
+# --nvtx_ranges: every timer interval is also an NVTX range (visible in nsys / ncu --nvtx); the
+# reference has no profiler integration at all.
+_NVTX = False
+
+
+def set_nvtx_ranges(on: bool):
+    global _NVTX
+    _NVTX = bool(on) and torch.cuda.is_available()
+
+
 class Timer(_Base):
     def __init__(self, name):
         super().__init__(name)
@@ -62,10 +72,14 @@ class Timer(_Base):
             self._start_evt.record()
         else:
             self._t0 = time.time()
+        if _NVTX:
+            torch.cuda.nvtx.range_push(self.name)
         self._started = True
 
     def stop(self, barrier=False):
         assert self._started, "timer is not started"
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
         if barrier and dist.is_initialized():
             dist.barrier(group=self._barrier_group)
         if self._cuda:

@@ -285,6 +285,10 @@ def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_sch
     timers("optimizer").stop()
     if update_successful:
         optimizer.gather_model_params(args, timers)
+        every = getattr(args, "check_dp_consistency_interval", 0)
+        if every and hasattr(optimizer, "check_dp_consistency") and \
+                (getattr(args, "curr_iteration", 0) + 1) % every == 0:
+            optimizer.check_dp_consistency()
         increment = get_num_microbatches() * args.micro_batch_size * args.data_parallel_size
         opt_param_scheduler.step(increment=increment)
         skipped = 0

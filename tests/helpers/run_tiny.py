@@ -36,6 +36,9 @@ def main():
     p.add_argument("--bucket_mb", type=int, default=None)
     p.add_argument("--fused_comm", default="auto")
     p.add_argument("--fused_dp", default="auto")
+    p.add_argument("--check_dp", type=int, default=0)
+    p.add_argument("--corrupt_rank", type=int, default=-1, help="test hook: perturb one parameter on this rank")
+    p.add_argument("--nvtx", action="store_true")
     a = p.parse_args()
 
     import torch
@@ -77,6 +80,10 @@ def main():
     if a.bucket_mb is not None:
         argv += ["--ddp_bucket_mb", str(a.bucket_mb)]
     argv += ["--b200_fused_comm", a.fused_comm, "--b200_fused_dp", a.fused_dp]
+    if a.check_dp:
+        argv += ["--check_dp_consistency_interval", str(a.check_dp)]
+    if a.nvtx:
+        argv.append("--nvtx_ranges")
     if a.recompute:
         argv += ["--recompute_granularity", "full", "--recompute_method", "uniform"]
     if a.vpp_layers:
@@ -108,6 +115,9 @@ def main():
     losses, norms = [], []
     for s in range(a.steps):
         args.curr_iteration = s
+        if s == 1 and a.corrupt_rank == int(os.environ.get("RANK", "0")):
+            with torch.no_grad():
+                next(model[0].parameters()).view(-1)[3] += 1.0
         ld, skipped, gn, _ = train_step(finetune.forward_step, data, model, optimizer, sched, args)
         if ld:
             losses.append(float(ld["lm loss"].item()))

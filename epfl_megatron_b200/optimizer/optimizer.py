@@ -449,6 +449,15 @@ class FlatOptimizer(MegatronOptimizer):
             return None
         return flat[loc[0]:loc[1]]
 
+    @staticmethod
+    def _layout_signature(ch):
+        """Order-sensitive fingerprint of (start, end) of every parameter in the flat buffer."""
+        h = 1469598103934665603
+        for _, s, e, _ in ch.layout:
+            for x in (s, e):
+                h = ((h ^ x) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+        return h
+
     def state_dict(self):
         sd = {"step": self.step_count,
               "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]}
@@ -461,6 +470,9 @@ class FlatOptimizer(MegatronOptimizer):
                                          for i, ch in enumerate(self.chunks)},
                                "param_groups": sd["param_groups"]}
             sd["shard_ranges"] = [(ch.shard_lo, ch.shard_hi, ch.N) for ch in self.chunks]
+            # the raw shards are only meaningful for the buffer order they were cut from (it changes
+            # with --b200_fused_dp, which rotates bucket owners): store a fingerprint of it
+            sd["layout_signature"] = [self._layout_signature(ch) for ch in self.chunks]
             return sd
         state, mains, idx = {}, [], 0
         for ch in self.chunks:
@@ -487,6 +499,13 @@ class FlatOptimizer(MegatronOptimizer):
                 lo, hi, n = sd["shard_ranges"][i]
                 assert (lo, hi, n) == (ch.shard_lo, ch.shard_hi, ch.N), \
                     "distributed-optimizer checkpoints can only be loaded with the same data-parallel size"
+                sig = sd.get("layout_signature")
+                if sig is not None and sig[i] != self._layout_signature(ch):
+                    raise RuntimeError(
+                        "distributed-optimizer checkpoint was written with a different parameter order in "
+                        "the flat buffers (different --b200_fused_dp / --ddp_bucket_mb setting or model "
+                        "structure); load it with the settings it was saved with, or load the model only "
+                        "(--no_load_optim)")
                 ch.main.copy_(sd["shard_fp32_from_float16_groups"][i])
                 ch.m.copy_(inner[i]["exp_avg"])
                 ch.v.copy_(inner[i]["exp_avg_sq"])

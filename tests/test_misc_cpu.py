@@ -83,3 +83,36 @@ def test_fused_dp_buffer_order_rotates_bucket_owners():
     assert [i for i, _, _ in out] == [0, 3, 4, 5, 8, 1, 2, 6, 7]
     assert [i for i, _, c in out if c] == [0, 3, 8, 1, 6]
     assert sorted(i for i, _, _ in out) == list(range(9))
+
+
+def test_bench_argument_sets_of_all_baseline_configs_validate(monkeypatch):
+    """bench.py's flag sets for the five BASELINE.json configurations parse and pass validate_args."""
+    import types
+
+    import bench
+    import finetune
+    from epfl_megatron_b200.arguments import parse_args, validate_args
+
+    def ns(**k):
+        d = dict(model="llama2-7b", steps=2, warmup=3, seq=4096, micro_batch=1, num_microbatches=4, recompute=False,
+                 debug_layers=0, tp=0, pp=1, vpp_layers=0)
+        d.update(k)
+        return types.SimpleNamespace(**d)
+
+    monkeypatch.setenv("WORLD_SIZE", "8")
+    monkeypatch.setenv("RANK", "0")
+    cases = [(ns(), (2, 4), {}),
+             (ns(model="llama2-13b", tp=4, pp=2, vpp_layers=5), (4, 1), {"virtual_pipeline_model_parallel_size": 4}),
+             (ns(model="falcon-40b", tp=8, seq=2048), (8, 1), {"parallel_attn": True, "use_rms_norm": False}),
+             (ns(model="llama2-70b", tp=4, pp=2, recompute=True), (4, 1), {"recompute_granularity": "full"})]
+    for a, layout, expect in cases:
+        tp, dp = bench.parallel_layout(8, a.model, a.tp, a.pp)
+        assert (tp, dp) == layout
+        argv, gbs = bench.build_arg_list(a, tp, dp)
+        assert gbs == 4 * dp
+        args = parse_args(finetune.extra_args, args_list=argv)
+        args.world_size, args.rank = 8, 0
+        args = validate_args(args, {})
+        assert args.sequence_parallel and args.use_distributed_optimizer and args.bf16
+        for k, v in expect.items():
+            assert getattr(args, k) == v, (a.model, k, getattr(args, k))

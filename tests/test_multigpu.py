@@ -58,6 +58,16 @@ def test_dp4_fused_with_tp2():
     _close(fused["losses"], nccl["losses"], 5e-3)
 
 
+def test_pp2_dp2_fused_dp_matches_nccl():
+    """Pipeline stages each run their own fused data-parallel reduction (one workspace per stage)."""
+    _need(4)
+    kw = dict(nproc=4, pp=2, steps=5, dist_opt=True, num_microbatches=4, bucket_mb=1, layers=4)
+    fused = run_tiny(fused_dp="on", check_dp=1, **kw)
+    nccl = run_tiny(fused_dp="off", **kw)
+    assert fused["fused_dp"]
+    _close(fused["losses"], nccl["losses"], 2e-3)
+
+
 def test_pp2_1f1b(single):
     _need(2)
     r = run_tiny(nproc=2, pp=2, steps=5, num_microbatches=4)

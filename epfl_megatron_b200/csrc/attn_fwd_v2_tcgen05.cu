@@ -157,35 +157,42 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // MMA issuer: the warp runs the loop in uniform control flow, descriptors live in uniform
+    // registers and advance by constants, only the tcgen05 instructions are predicated on the
+    // elected lane (a 128 x 128 x 16 MMA occupies the tensor pipe for 64 cycles: the issue path
+    // has to be shorter than that).
+    {
+      const bool leader = elect_one_sync();
       constexpr uint32_t idesc_s = make_idesc_bf16(kF2T, kF2T, 0, 0);
       constexpr uint32_t idesc_o = make_idesc_bf16(kF2T, kF2T, 0, 1);
-      const uint32_t aQ = smem_u32(smem + F2Smem::kQ), aK = smem_u32(smem + F2Smem::kK);
-      const uint32_t aV = smem_u32(smem + F2Smem::kV);
+      const uint64_t dQ = make_sw128_desc(smem_u32(smem + F2Smem::kQ), 16, 1024);
+      const uint64_t dK = make_sw128_desc(smem_u32(smem + F2Smem::kK), 16, 1024);
+      const uint64_t dV = make_sw128_desc(smem_u32(smem + F2Smem::kV), kF2Box, 1024);
       auto issue_s = [&](int t, int i) {      // S_t = Q_t K_i^T
-        const uint32_t q = aQ + t * kF2Tile, k = aK + (i & 1) * kF2Tile;
+        const uint64_t q = dQ + static_cast<uint64_t>((t * kF2Tile) >> 4);
+        const uint64_t k = dK + static_cast<uint64_t>(((i & 1) * kF2Tile) >> 4);
 #pragma unroll
         for (int kk = 0; kk < kF2T / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * kF2Box + (kk & 3) * 32;
-          umma_bf16_ss(tmem_base + t * 128, make_sw128_desc(q + off, 16, 1024),
-                       make_sw128_desc(k + off, 16, 1024), idesc_s, kk != 0);
+          const uint64_t off = static_cast<uint64_t>(((kk >> 2) * kF2Box + (kk & 3) * 32) >> 4);
+          if (leader) umma_bf16_ss(tmem_base + t * 128, q + off, k + off, idesc_s, kk != 0);
         }
-        umma_commit(&s_full[t]);
+        if (leader) umma_commit(&s_full[t]);
       };
       auto issue_pv = [&](int t, int i) {     // O_t += P_t V_i, P from TMEM
-        const uint32_t v = aV + (i & 1) * kF2Tile;
+        const uint64_t v = dV + static_cast<uint64_t>(((i & 1) * kF2Tile) >> 4);
 #pragma unroll
         for (int kk = 0; kk < kF2T / 16; ++kk)
-          f2_umma_ts(tmem_base + 256 + t * 128, tmem_base + t * 128 + kk * 8,
-                     make_sw128_desc(v + kk * 2048, kF2Box, 1024), idesc_o, (i | kk) != 0);
-        umma_commit(&o_done[t]);
+          if (leader)
+            f2_umma_ts(tmem_base + 256 + t * 128, tmem_base + t * 128 + kk * 8,
+                       v + static_cast<uint64_t>((kk * 2048) >> 4), idesc_o, (i | kk) != 0);
+        if (leader) umma_commit(&o_done[t]);
       };
       mbar_wait(q_full, 0);
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
       issue_s(0, 0);
       issue_s(1, 0);
-      umma_commit(&k_empty[0]);
+      if (leader) umma_commit(&k_empty[0]);
       for (int i = 0; i < n_max; ++i) {
         const int st = i & 1;
 #pragma unroll
@@ -195,12 +202,12 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           mbar_wait(&v_full[st], (i >> 1) & 1);
           tc_fence_after();
           issue_pv(t, i);
-          if (t == 1) umma_commit(&v_empty[st]);
+          if (t == 1 && leader) umma_commit(&v_empty[st]);
           if (i + 1 < nb[t]) {
             mbar_wait(&k_full[st ^ 1], ((i + 1) >> 1) & 1);
             tc_fence_after();
             issue_s(t, i + 1);
-            if (t == 1) umma_commit(&k_empty[st ^ 1]);
+            if (t == 1 && leader) umma_commit(&k_empty[st ^ 1]);
           }
         }
       }

@@ -356,6 +356,19 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr, uint32_t
   return d;
 }
 
+// True in exactly one lane of a converged warp. MMA-issuing warps walk their loops in uniform
+// control flow (descriptors stay in uniform registers, advanced by constants) and predicate only
+// the tcgen05 instructions on this: a handful of instructions per MMA instead of ~20.
+__device__ __forceinline__ bool elect_one_sync() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // Instruction descriptor for kind::f16 with bf16 A/B and fp32 D.
 //   c_format [4,6)=1 (F32), a_format [7,10)=1 (BF16), b_format [10,13)=1 (BF16),
 //   a_major bit 15, b_major bit 16 (0 = K-major, 1 = MN-major),

@@ -6,6 +6,7 @@ the ``--b200_kernels`` flag); it is a test switch, not a second backend.
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 
@@ -436,6 +437,9 @@ class _AttnFusedQKVFn(torch.autograd.Function):
 
 _ATTN_BWD = "own"   # own | fa2
 _ATTN_FWD_ENTRY = "b200_attn_fwd_v2"   # two query tiles per CTA; "b200_attn_fwd" = first generation
+# "b200_attn_bwd" = first generation (one S / dP buffer, 128-row streamed tiles);
+# "b200_attn_bwd_v2" = 64-row streamed blocks with S / dP double-buffered in TMEM
+_ATTN_BWD_ENTRY = os.environ.get("B200_ATTN_BWD_ENTRY", "b200_attn_bwd")
 
 
 def set_attn_bwd_mode(mode: str):
@@ -444,7 +448,7 @@ def set_attn_bwd_mode(mode: str):
     _ATTN_BWD = mode
 
 
-def attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal=True):
+def attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal=True, entry=None):
     """dqkv (same layout as qkv: [s, b, g, q_per_g+2, hn]) <- attention backward, own tcgen05
     kernels (csrc/attn_bwd_tcgen05.cu). out/dout: [s, b, np*hn] contiguous, lse [b, np, s]."""
     s, b, g, nslot, hn = qkv.shape
@@ -454,7 +458,7 @@ def attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal=True):
     ss, sb, sg, sj = qkv.stride(0), qkv.stride(1), qkv.stride(2), qkv.stride(3)
     ds, db, dg, dj = dqkv.stride(0), dqkv.stride(1), dqkv.stride(2), dqkv.stride(3)
     base, dbase = qkv.data_ptr(), dqkv.data_ptr()
-    L.call("b200_attn_bwd", base, base + qpg * sj * 2, base + (qpg + 1) * sj * 2, out.data_ptr(),
+    L.call(entry or _ATTN_BWD_ENTRY, base, base + qpg * sj * 2, base + (qpg + 1) * sj * 2, out.data_ptr(),
            dout.data_ptr(), lse.data_ptr(), dbase, dbase + qpg * dj * 2, dbase + (qpg + 1) * dj * 2,
            scratch.data_ptr(), s, s, b, g, qpg, hn, ss, sb, sg, sj, ss, sb, sg, ds, db, dg, dj,
            ds, db, dg, float(scale), int(causal), L.stream_ptr(), launches=3)

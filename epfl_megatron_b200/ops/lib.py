@@ -53,6 +53,9 @@ _SIGNATURES = {
     "b200_attn_bwd": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
                        i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64,
                        f32, i32, vp], i32),
+    "b200_attn_bwd_v2": ([vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32,
+                          i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64, i64,
+                          f32, i32, vp], i32),
     "b200_symm_alloc": ([i64, vp], i32),
     "b200_symm_free": ([vp], i32),
     "b200_symm_export": ([vp, vp], i32),

@@ -412,7 +412,7 @@ def check_attn_fwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True, entry=None):
     return st
 
 
-def check_attn_bwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True):
+def check_attn_bwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True, entry=None):
     """Own backward vs autograd through the fp32 restatement of the same attention."""
     from . import functional as Fn
     dev = _dev()
@@ -422,7 +422,7 @@ def check_attn_bwd(S=512, B=2, G=2, QPG=4, HN=128, causal=True):
     scale = 1.0 / math.sqrt(HN)
     out, lse = attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, causal)
     dqkv = torch.full_like(qkv, float("nan"))
-    Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal)
+    Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, causal, entry=entry)
     ref_in = qkv.float().requires_grad_()
     q = ref_in[:, :, :, :QPG].reshape(S, B, G * QPG, HN)
     ro, _ = attn_ref(q, ref_in[:, :, :, QPG], ref_in[:, :, :, QPG + 1], scale, causal)
@@ -482,6 +482,12 @@ CHECKS = {
     "attn_bwd_mqa_long": lambda: check_attn_bwd(1024, 1, 1, 8, 128, True),
     "attn_bwd_full": lambda: check_attn_bwd(384, 1, 2, 2, 128, False),
     "attn_bwd_ragged": lambda: check_attn_bwd(328, 1, 1, 2, 128, True),
+    "attn_bwd2_small": lambda: check_attn_bwd(128, 1, 1, 1, 128, True, entry="b200_attn_bwd_v2"),
+    "attn_bwd2_mha": lambda: check_attn_bwd(512, 2, 4, 1, 128, True, entry="b200_attn_bwd_v2"),
+    "attn_bwd2_gqa": lambda: check_attn_bwd(entry="b200_attn_bwd_v2"),
+    "attn_bwd2_mqa_long": lambda: check_attn_bwd(1024, 1, 1, 8, 128, True, entry="b200_attn_bwd_v2"),
+    "attn_bwd2_full": lambda: check_attn_bwd(384, 1, 2, 2, 128, False, entry="b200_attn_bwd_v2"),
+    "attn_bwd2_ragged": lambda: check_attn_bwd(328, 1, 1, 2, 128, True, entry="b200_attn_bwd_v2"),
 }
 
 

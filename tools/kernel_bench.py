@@ -141,9 +141,17 @@ def bench_attn_bwd():
         out, lse = SC.attn_fwd_fused_qkv(qkv, G, QPG, HN, scale, True)
         dqkv = torch.empty_like(qkv)
         fl = 10.0 * S * S * G * QPG * HN * B / 2     # 5 GEMMs of the single-pass formulation
-        t_own = timeit(lambda: Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, True))
+        t_own = timeit(lambda: Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, True,
+                                                     entry="b200_attn_bwd"))
         rec = dict(kernel="attn_bwd", shape=name, S=S, heads=G * QPG, kv_heads=G, ms_own=t_own,
                    tflops_own_5gemm_equiv=fl / t_own / 1e9)
+        if os.environ.get("B200_BENCH_ATTN_BWD_V2", "1") == "1":
+            try:
+                t_v2 = timeit(lambda: Fn.attn_bwd_fused_qkv(qkv, out, dout, lse, dqkv, scale, True,
+                                                            entry="b200_attn_bwd_v2"))
+                rec.update(ms_own_v2=t_v2, tflops_own_v2_5gemm_equiv=fl / t_v2 / 1e9)
+            except Exception as e:  # noqa: BLE001
+                rec.update(v2_error=str(e)[:200])
         try:
             k = qkv[:, :, :, QPG].permute(1, 0, 2, 3)
             v = qkv[:, :, :, QPG + 1].permute(1, 0, 2, 3)

@@ -92,6 +92,7 @@ class DistributedDataParallel(DistributedDataParallelBase):
         # fp32 buffers live in peer-mappable memory; the distributed optimizer attaches a
         # DPWorkspace per buffer and the reduction becomes the in-kernel reduce-scatter
         self.fused_dp = fused_dp
+        self.fused_dp_required = False        # set by the caller for --b200_fused_dp on
         self._dp_ws = {}
         self._reduced = False
         self.bucket_bytes = int(bucket_mb * (1 << 20))

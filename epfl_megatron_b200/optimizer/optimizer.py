@@ -91,9 +91,24 @@ class _Chunk:
         self.v = torch.zeros(n, dtype=torch.float32, device=dev)
         if fused:
             bks = ddp.buckets_of(dtype)
-            self.ws = DPWorkspace(mpu.get_data_parallel_group(), self.grad, self.param, len(bks),
-                                  max(b.end - b.start for b in bks))
-            ddp.attach_dp_workspace(dtype, self.ws)
+            grp = mpu.get_data_parallel_group()
+            ws, err = None, ""
+            try:
+                ws = DPWorkspace(grp, self.grad, self.param, len(bks), max(b.end - b.start for b in bks))
+            except Exception as e:  # noqa: BLE001 - e.g. CUDA IPC not permitted in this container
+                err = f"{type(e).__name__}: {e}"
+            # every rank of the group must take the same path
+            ok = torch.tensor([1 if ws is not None else 0], device=dev, dtype=torch.int32)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=grp)
+            if int(ok.item()) == 1:
+                self.ws = ws
+                ddp.attach_dp_workspace(dtype, self.ws)
+            else:
+                if getattr(ddp, "fused_dp_required", False):
+                    raise RuntimeError(f"--b200_fused_dp on: peer-mapped workspace could not be created ({err})")
+                if dist.get_rank() == 0:
+                    print(f"WARNING: fused data-parallel path disabled, falling back to NCCL ({err or 'a peer failed'})",
+                          flush=True)
 
     def local(self, lo, hi):
         """Intersection of [lo, hi) with the owned shard, in shard-local coordinates."""

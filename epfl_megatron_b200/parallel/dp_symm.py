@@ -50,21 +50,40 @@ def group_on_one_host(group) -> bool:
     return len(set(names)) == 1
 
 
-def _exchange(group, ptr: int):
-    """Export a local allocation, import the peers' ones: base address per rank of the group."""
+def _exchange(group, make_ptrs):
+    """Export local allocations and import the peers' ones: for each allocation the base address per
+    rank of the group. ``make_ptrs()`` returns the local device pointers (it may allocate). The one
+    collective in here is reached by every rank even when a local step failed, so that a failure on
+    one rank (CUDA IPC not permitted, out of memory) surfaces as an exception on ALL ranks instead of
+    a hang."""
     rank, n = dist.get_rank(group), dist.get_world_size(group)
-    handle = (C.c_ubyte * 64)()
-    L.call("b200_symm_export", ptr, handle, launches=0)
-    handles = [None] * n
-    dist.all_gather_object(handles, bytes(handle), group=group)
+    ptrs, mine, err = None, None, None
+    try:
+        ptrs = make_ptrs()
+        mine = []
+        for ptr in ptrs:
+            handle = (C.c_ubyte * 64)()
+            L.call("b200_symm_export", ptr, handle, launches=0)
+            mine.append(bytes(handle))
+    except Exception as e:  # noqa: BLE001
+        err, mine = e, None
+    everyone = [None] * n
+    dist.all_gather_object(everyone, mine, group=group)
+    if err is not None:
+        raise err
+    if any(h is None for h in everyone):
+        raise RuntimeError("a peer could not export its buffers")
     out = []
-    for r, h in enumerate(handles):
-        if r == rank:
-            out.append(ptr)
-            continue
-        p = C.c_void_p()
-        L.call("b200_symm_import", (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p), launches=0)
-        out.append(p.value)
+    for i, ptr in enumerate(ptrs):
+        bases = []
+        for r in range(n):
+            if r == rank:
+                bases.append(ptr)
+                continue
+            p = C.c_void_p()
+            L.call("b200_symm_import", (C.c_ubyte * 64).from_buffer_copy(everyone[r][i]), C.byref(p), launches=0)
+            bases.append(p.value)
+        out.append(bases)
     return out
 
 
@@ -82,11 +101,13 @@ class DPWorkspace:
         self.shard_lo, self.shard_hi = self.rank * self.shard, (self.rank + 1) * self.shard
         self.device = grad.device
         self.n_buckets = n_buckets
-        self.flags = symm_tensor((n_buckets + 1) * self.dp + 8, torch.int32, self.device)
-        self.peer_grad = _exchange(group, grad.data_ptr())
-        self.peer_param = _exchange(group, param.data_ptr())
-        self.peer_flags = _exchange(group, self.flags.data_ptr())
-        dist.barrier(group=group)
+        def local_buffers():
+            self.flags = symm_tensor((n_buckets + 1) * self.dp + 8, torch.int32, self.device)
+            return [grad.data_ptr(), param.data_ptr(), self.flags.data_ptr()]
+
+        # the caller follows up with a collective agreement (optimizer._Chunk), which is also the
+        # barrier that orders "everyone has mapped everyone" before the first kernel
+        self.peer_grad, self.peer_param, self.peer_flags = _exchange(group, local_buffers)
         self.epoch = 0          # one per training step (bucket flags)
         self.param_epoch = 0    # one per successful optimizer step
         self.side = torch.cuda.Stream(device=self.device)

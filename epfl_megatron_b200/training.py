@@ -180,6 +180,8 @@ def get_model(model_provider_func, model_type=ModelType.encoder_or_decoder, wrap
                               fuse_wgrad=args.gradient_accumulation_fusion, group_key_fn=key_fn,
                               overlap_grad_reduce=getattr(args, "overlap_grad_reduce", True),
                               bucket_mb=getattr(args, "ddp_bucket_mb", 256), fused_dp=fused_dp) for m in model]
+            for m in model:
+                m.fused_dp_required = fused_dp and getattr(args, "b200_fused_dp", "auto") == "on"
             if args.data_parallel_random_init:
                 for m in model:
                     m.broadcast_params()

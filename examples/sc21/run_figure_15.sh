@@ -1,0 +1,11 @@
+#!/bin/bash
+# Tensor vs data parallelism on 64 GPUs: bash run_figure_15.sh <TP: 2|4|8|16|32> <GBS: 32|128|512>   (DP = 64 / TP, PP 1)
+set -euo pipefail
+. "$(dirname "$0")/CONFIG.sh"
+TP=${1:?tensor-parallel size}; GBS=${2:-32}
+PP=1; MBS=1; NLS=32; HS=3840; NAH=32; NNODES=8
+export NNODES
+export OPTIONS="--tensor_model_parallel_size $TP --pipeline_model_parallel_size $PP --micro_batch_size $MBS \
+ --global_batch_size $GBS --num_layers $NLS --hidden_size $HS --num_attention_heads $NAH \
+ --DDP_impl local ${EXTRA:-} $COMMON"
+. "$(dirname "$0")/SBATCH.sh"

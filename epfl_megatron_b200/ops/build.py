@@ -105,5 +105,8 @@ def build_all(force: bool = False, verbose: bool = False):
 if __name__ == "__main__":
     force = "--force" in sys.argv
     verbose = "-v" in sys.argv
-    for p in build_all(force, verbose):
-        print("built", p)
+    if "--data-only" in sys.argv:       # CPU index builders only (no nvcc needed): tokenisation hosts
+        print("built", build_data_helpers(force))
+    else:
+        for p in build_all(force, verbose):
+            print("built", p)

@@ -16,6 +16,7 @@ Public surface of megatron/core/tensor_parallel/layers.py:41-701. What differs i
 from __future__ import annotations
 
 import math
+import os
 from typing import Callable, Optional
 
 import torch
@@ -241,6 +242,17 @@ class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
 _FUSED_COMM = "auto"    # auto | on | off  (--b200_fused_comm)
 
 
+# Per-op policy of "auto": the in-kernel all-gather is used up to this tensor-parallel size. At tp 8
+# its copier warps still walk the 7 peers one after another and NCCL all-gather + GEMM is faster
+# (0.119 vs 0.175 ms on the Falcon-40B shapes); the in-kernel reduce-scatter wins at
+# every size and stays on. "--b200_fused_comm on" forces both.
+_FUSED_AG_MAX_TP = int(os.environ.get("B200_FUSED_AG_MAX_TP", "4"))
+
+
+def _fused_all_gather(tp: int) -> bool:
+    return _FUSED_COMM == "on" or tp <= _FUSED_AG_MAX_TP
+
+
 def set_fused_comm_mode(mode: str):
     global _FUSED_COMM
     assert mode in ("auto", "on", "off")
@@ -300,7 +312,12 @@ class _FusedColumnSP(torch.autograd.Function):
             x2 = x2.contiguous()
         tp = state.get_tensor_model_parallel_world_size()
         ws = _workspace(x2.shape[0] * tp, K, K)
-        out, gathered = ws.allgather_gemm(x2, weight)
+        if _fused_all_gather(tp):
+            out, gathered = ws.allgather_gemm(x2, weight)
+        else:
+            gathered = torch.empty(x2.shape[0] * tp, K, dtype=x2.dtype, device=x2.device)
+            all_gather_into(gathered, x2, state.get_tensor_model_parallel_group())
+            out = Fn.gemm_nt(gathered, weight)
         ctx.save_for_backward(gathered, weight)
         ctx.weight_ref = weight
         ctx.gaf = gradient_accumulation_fusion
@@ -350,7 +367,12 @@ class _FusedRowSP(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         ws = _workspace(x2.shape[0], N, N)
-        dx, gathered_dy = ws.allgather_gemm(dy2, weight, b_mn_major=True)  # [M, K/tp], [M, N]
+        if _fused_all_gather(state.get_tensor_model_parallel_world_size()):
+            dx, gathered_dy = ws.allgather_gemm(dy2, weight, b_mn_major=True)  # [M, K/tp], [M, N]
+        else:
+            gathered_dy = torch.empty(x2.shape[0], N, dtype=dy2.dtype, device=dy2.device)
+            all_gather_into(gathered_dy, dy2, state.get_tensor_model_parallel_group())
+            dx = Fn.gemm_nn(gathered_dy, weight)
         gw = _accumulate_wgrad(ctx.weight_ref, gathered_dy, x2, ctx.gaf)
         return dx.view(ctx.in_shape), gw, None
 

@@ -407,9 +407,12 @@ def validate_args(args, defaults=None):
         _require(args.recompute_method is None, "recompute method not supported with selective")
     if not args.parallel_attn:
         _require(not args.parallel_layernorm, "parallel_layernorm only implemented with parallel_attn")
-    if args.num_attention_heads_kv % args.tensor_model_parallel_size != 0 and \
-            args.num_attention_heads_kv != 1:
-        raise AssertionError("num_attention_heads_kv must be divisible by tensor parallel size")
+    # The fused QKV weight is sharded by KV group, so every tensor-parallel
+    # rank needs whole groups: multi-query models (one KV head) run with tp 1, as in the reference,
+    # whose [s, b, -1, q_per_group + 2, hn] view (transformer.py:448) breaks the same way.
+    _require(args.num_attention_heads_kv % args.tensor_model_parallel_size == 0,
+             f"num_attention_heads_kv ({args.num_attention_heads_kv}) must be divisible by the tensor-parallel "
+             f"size ({args.tensor_model_parallel_size})")
 
     if args.tensor_model_parallel_size == 1:
         args.sequence_parallel = False

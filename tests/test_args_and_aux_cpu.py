@@ -53,7 +53,9 @@ def test_interleaving_allowed_for_two_stages():
 def test_gqa_recompute_and_misc_rules():
     with pytest.raises(AssertionError):
         _args(["--num_attention_heads_kv", "2", "--tensor_model_parallel_size", "4"])
-    assert _args(["--num_attention_heads_kv", "1", "--tensor_model_parallel_size", "4"]).num_attention_heads_kv == 1
+    with pytest.raises(AssertionError):                                     # multi-query needs tp 1
+        _args(["--num_attention_heads_kv", "1", "--tensor_model_parallel_size", "4"])
+    assert _args(["--num_attention_heads_kv", "1"]).num_attention_heads_kv == 1
     with pytest.raises(AssertionError):
         _args(["--recompute_granularity", "selective", "--recompute_method", "uniform"])
     with pytest.raises(AssertionError):

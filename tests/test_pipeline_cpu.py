@@ -53,3 +53,11 @@ def test_dp_consistency_check_passes_and_catches_divergence():
     # all-gather; the replicated optimizer keeps it)
     with pytest.raises(AssertionError, match="replicas diverged"):
         run_tiny(nproc=2, env_extra=ENV, corrupt_rank=1, **dict(kw, dist_opt=False))
+
+
+def test_falcon_gqa_tp2_matches_single_process():
+    """Falcon block (parallel attention + MLP, two LayerNorms, GeLU, tied embeddings) with grouped KV
+    heads sharded over two tensor-parallel ranks under sequence parallelism."""
+    kw = dict(KW, model_name="falcon", layers=2, num_microbatches=2)
+    one = run_tiny(env_extra=ENV, **kw)["losses"]
+    _close(run_tiny(nproc=2, tp=2, env_extra=ENV, **kw)["losses"], one, 2e-3)

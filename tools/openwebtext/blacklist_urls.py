@@ -54,6 +54,8 @@ def is_bad(url):
 
 if __name__ == "__main__":
     t0 = time.time()
+    if len(sys.argv) < 3 or sys.argv[1] in ("-h", "--help"):
+        sys.exit("usage: python tools/openwebtext/blacklist_urls.py <directory with url files> <output file of clean urls>")
     path, out = sys.argv[1], sys.argv[2]
     seen, counts = set(), {}
     for fname in sorted(glob.glob(path + "/*.txt")):

@@ -53,4 +53,6 @@ def filter_corpus(filename, out_filename, print_interval=10000, tokenize=None):
 
 
 if __name__ == "__main__":
+    if len(sys.argv) < 3 or sys.argv[1] in ("-h", "--help"):
+        sys.exit("usage: python tools/openwebtext/cleanup_dataset.py <input jsonl> <output jsonl>")
     filter_corpus(sys.argv[1], sys.argv[2])

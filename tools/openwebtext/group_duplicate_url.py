@@ -6,6 +6,8 @@ import time
 
 if __name__ == "__main__":
     t0 = time.time()
+    if len(sys.argv) < 3 or sys.argv[1] in ("-h", "--help"):
+        sys.exit("usage: python tools/openwebtext/group_duplicate_url.py <similar-url pairs file> <output groups jsonl> [jaccard threshold = 0.7]")
     inp, out = sys.argv[1], sys.argv[2]
     thr = float(sys.argv[3]) if len(sys.argv) > 3 else 0.7
     parent = {}

@@ -5,6 +5,8 @@ import sys
 import time
 
 if __name__ == "__main__":
+    if len(sys.argv) < 4 or sys.argv[1] in ("-h", "--help"):
+        sys.exit("usage: python tools/openwebtext/remove_group_duplicates.py <url groups jsonl> <data jsonl> <output jsonl>")
     groups, data, out = sys.argv[1], sys.argv[2], sys.argv[3]
     t0 = time.time()
     drop = set()

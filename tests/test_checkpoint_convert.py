@@ -178,3 +178,67 @@ def test_loader_saver_plugins_match_direct_reshard(tmp_path):
             assert fd.keys() == fv.keys()
             for k in fd:
                 assert torch.equal(fd[k], fv[k]), k
+
+
+def test_meta_shards_merge_and_convert_like_the_hf_route(tmp_path):
+    """Meta's model-parallel ``consolidated.NN.pth`` shards are merged along Meta's per-key dimensions,
+    and the Meta route (weights already in interleaved-pair RoPE order) produces the same Megatron
+    tensors as the HF route (half-rotation order, permuted on the way in)."""
+    import sys as _sys
+    _sys.path.insert(0, os.path.join(ROOT, "weights2megatron"))
+    try:
+        import merge_llama as ml
+        import weights2megatron as w2m
+    finally:
+        _sys.path.pop(0)
+    from epfl_megatron_b200.utils.ckpt_convert import rope_hf_to_interleaved
+    torch.manual_seed(3)
+    n_layer, hidden, n_heads, n_kv, ffn, vocab = 2, 64, 4, 2, 96, 128
+    hn = hidden // n_heads
+    hf = {"model.embed_tokens.weight": torch.randn(vocab, hidden), "model.norm.weight": torch.randn(hidden),
+          "lm_head.weight": torch.randn(vocab, hidden)}
+    for i in range(n_layer):
+        p = f"model.layers.{i}"
+        hf.update({f"{p}.self_attn.q_proj.weight": torch.randn(n_heads * hn, hidden),
+                   f"{p}.self_attn.k_proj.weight": torch.randn(n_kv * hn, hidden),
+                   f"{p}.self_attn.v_proj.weight": torch.randn(n_kv * hn, hidden),
+                   f"{p}.self_attn.o_proj.weight": torch.randn(hidden, hidden),
+                   f"{p}.mlp.gate_proj.weight": torch.randn(ffn, hidden), f"{p}.mlp.up_proj.weight": torch.randn(ffn, hidden),
+                   f"{p}.mlp.down_proj.weight": torch.randn(hidden, ffn),
+                   f"{p}.input_layernorm.weight": torch.randn(hidden),
+                   f"{p}.post_attention_layernorm.weight": torch.randn(hidden),
+                   f"{p}.self_attn.rotary_emb.inv_freq": torch.randn(hn // 2)})
+    named = ml.hf_state_to_meta(hf)
+    assert "layers.1.feed_forward.w3.weight" in named and not any("rotary" in k for k in named)
+    # the same model as Meta would publish it: q/k rows in interleaved-pair order
+    meta = dict(named)
+    for i in range(n_layer):
+        meta[f"layers.{i}.attention.wq.weight"] = rope_hf_to_interleaved(named[f"layers.{i}.attention.wq.weight"], n_heads, hn)
+        meta[f"layers.{i}.attention.wk.weight"] = rope_hf_to_interleaved(named[f"layers.{i}.attention.wk.weight"], n_kv, hn)
+    meta["rope.freqs"] = torch.randn(hn // 2)
+    # cut into two model-parallel shards the way Meta does
+    col = ("wq", "wk", "wv", "w1", "w3", "output")              # split along dim 0
+    row = ("wo", "w2", "tok_embeddings")                       # split along the last dim
+    shards = [{}, {}]
+    for k, v in meta.items():
+        short = k.split(".")[-2] if "." in k else k
+        for r in range(2):
+            if short in col:
+                shards[r][k] = v.chunk(2, dim=0)[r].clone()
+            elif short in row:
+                shards[r][k] = v.chunk(2, dim=-1)[r].clone()
+            else:
+                shards[r][k] = v.clone()
+    for r in range(2):
+        torch.save(shards[r], tmp_path / f"consolidated.{r:02d}.pth")
+    merged, source = ml.merge_llama(7, 2, root_dir=str(tmp_path))
+    assert source == "meta" and set(merged) == set(meta)
+    for k in meta:
+        assert torch.equal(merged[k], meta[k]), k
+    via_meta = w2m.llama_to_megatron(merged, n_layer, hidden, n_heads, n_kv, source="meta")
+    via_hf = w2m.llama_to_megatron(named, n_layer, hidden, n_heads, n_kv, source="hf")
+    for k in via_hf["encoder"]:
+        assert torch.equal(via_meta["encoder"][k], via_hf["encoder"][k]), k
+    assert torch.equal(via_meta["lm_head"], hf["lm_head.weight"])
+    glu = via_hf["encoder"]["layers.0.mlp.dense_h_to_4h.weight"]
+    assert torch.equal(glu[:ffn], hf["model.layers.0.mlp.up_proj.weight"])      # [up; gate]

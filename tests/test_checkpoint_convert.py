@@ -2,6 +2,7 @@
 which needs real Llama-2 weights): HF layout -> Megatron release checkpoint -> shard to
 tp2/pp2 -> unshard -> HF layout must be bit-exact, and the Megatron model built from the
 converted checkpoint must reproduce the HF model's logits (reference gate: <= 1e-3 in fp32)."""
+import json
 import os
 import subprocess
 import sys
@@ -242,3 +243,49 @@ def test_meta_shards_merge_and_convert_like_the_hf_route(tmp_path):
     assert torch.equal(via_meta["lm_head"], hf["lm_head.weight"])
     glu = via_hf["encoder"]["layers.0.mlp.dense_h_to_4h.weight"]
     assert torch.equal(glu[:ffn], hf["model.layers.0.mlp.up_proj.weight"])      # [up; gate]
+
+
+def test_meta_llama_to_hf_cli(tmp_path):
+    """weights2megatron/convert_llama2hf.py: two Meta shards + params.json -> a HF directory whose
+    weights equal the HF model the shards were derived from."""
+    transformers = pytest.importorskip("transformers")
+    from epfl_megatron_b200.utils.ckpt_convert import rope_hf_to_interleaved
+    torch.manual_seed(5)
+    cfg = transformers.LlamaConfig(hidden_size=64, intermediate_size=96, num_attention_heads=4, num_key_value_heads=2,
+                                   num_hidden_layers=2, vocab_size=128, rms_norm_eps=1e-5, tie_word_embeddings=False)
+    hf = transformers.LlamaForCausalLM(cfg).float()
+    sd = {k: v.detach().clone() for k, v in hf.state_dict().items() if "rotary" not in k}
+    hn = 16
+    meta = {"tok_embeddings.weight": sd["model.embed_tokens.weight"], "norm.weight": sd["model.norm.weight"],
+            "output.weight": sd["lm_head.weight"], "rope.freqs": torch.zeros(hn // 2)}
+    names = {"self_attn.q_proj": "attention.wq", "self_attn.k_proj": "attention.wk", "self_attn.v_proj": "attention.wv",
+             "self_attn.o_proj": "attention.wo", "mlp.gate_proj": "feed_forward.w1", "mlp.down_proj": "feed_forward.w2",
+             "mlp.up_proj": "feed_forward.w3", "input_layernorm": "attention_norm",
+             "post_attention_layernorm": "ffn_norm"}
+    for i in range(2):
+        for h, m in names.items():
+            w = sd[f"model.layers.{i}.{h}.weight"]
+            if m == "attention.wq":
+                w = rope_hf_to_interleaved(w, 4, hn)
+            elif m == "attention.wk":
+                w = rope_hf_to_interleaved(w, 2, hn)
+            meta[f"layers.{i}.{m}.weight"] = w
+    src = tmp_path / "meta"
+    src.mkdir()
+    col, row = ("wq", "wk", "wv", "w1", "w3", "output"), ("wo", "w2", "tok_embeddings")
+    for r in range(2):
+        shard = {}
+        for k, v in meta.items():
+            short = k.split(".")[-2] if "." in k else k
+            shard[k] = (v.chunk(2, dim=0)[r] if short in col else v.chunk(2, dim=-1)[r] if short in row else v).clone()
+        torch.save(shard, src / f"consolidated.{r:02d}.pth")
+    (src / "params.json").write_text(json.dumps({"dim": 64, "n_layers": 2, "n_heads": 4, "n_kv_heads": 2,
+                                                 "norm_eps": 1e-5, "vocab_size": -1}))
+    out = tmp_path / "hf_out"
+    _run(["weights2megatron/convert_llama2hf.py", "--input_dir", str(src), "--model_size", "13",
+          "--output_dir", str(out)])
+    back = transformers.LlamaForCausalLM.from_pretrained(str(out), torch_dtype=torch.float32)
+    got = back.state_dict()
+    for k, v in sd.items():
+        assert torch.equal(got[k], v), k
+    assert back.config.num_key_value_heads == 2 and back.config.intermediate_size == 96

@@ -23,7 +23,7 @@ def run_tiny(nproc=1, timeout=600, env_extra=None, **kw):
         if v is True:
             flags.append(f"--{k}")
         elif v is not None and v is not False:
-            flags += [f"--{k}", str(v)]
+            flags.append(f"--{k}={v}")        # "=" form: values may themselves start with "--"
     env = dict(os.environ)
     env["MASTER_ADDR"] = "127.0.0.1"
     env["MASTER_PORT"] = str(free_port())

@@ -39,6 +39,8 @@ def main():
     p.add_argument("--check_dp", type=int, default=0)
     p.add_argument("--corrupt_rank", type=int, default=-1, help="test hook: perturb one parameter on this rank")
     p.add_argument("--nvtx", action="store_true")
+    p.add_argument("--no_sp", action="store_true", help="tensor parallel without sequence parallelism")
+    p.add_argument("--extra", default="", help="more training flags, space separated")
     a = p.parse_args()
 
     import torch
@@ -71,8 +73,9 @@ def main():
         argv += ["--parallel_attn", "--parallel_layernorm"]
     if a.dtype == "bf16":
         argv.append("--bf16")
-    if a.tp > 1:
+    if a.tp > 1 and not a.no_sp:
         argv.append("--sequence_parallel")
+    argv += a.extra.split()
     if a.dist_opt:
         argv.append("--use_distributed_optimizer")
     if a.no_overlap:

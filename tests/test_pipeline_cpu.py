@@ -61,3 +61,21 @@ def test_falcon_gqa_tp2_matches_single_process():
     kw = dict(KW, model_name="falcon", layers=2, num_microbatches=2)
     one = run_tiny(env_extra=ENV, **kw)["losses"]
     _close(run_tiny(nproc=2, tp=2, env_extra=ENV, **kw)["losses"], one, 2e-3)
+
+
+def test_tp2_without_sequence_parallel_and_distributed_saved_activations(base):
+    """Plain tensor parallelism (all-reduce instead of all-gather / reduce-scatter) under full
+    recompute with the checkpointed layer inputs sharded over the TP ranks
+    (--distribute_saved_activations, megatron/core/tensor_parallel/random.py:198-218): the CPU
+    initialisation is TP-invariant, so the losses match the single-process run to rounding."""
+    got = run_tiny(nproc=2, tp=2, no_sp=True, recompute=True, extra="--distribute_saved_activations",
+                   env_extra=ENV, **KW)["losses"]
+    _close(got, base, 1e-5)
+
+
+def test_pp2_standalone_embedding_stage(base):
+    """--standalone_embedding_stage: the first pipeline rank holds only the embedding, the
+    transformer layers all live on the second."""
+    got = run_tiny(nproc=2, pp=2, extra="--standalone_embedding_stage", env_extra=ENV, **KW)["losses"]
+    _close(got, base, 2e-3)
+    assert got[-1] < got[0]

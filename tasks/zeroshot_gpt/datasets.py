@@ -73,6 +73,10 @@ class _LambadaDataset(torch.utils.data.Dataset):
         tokens, labels = list(self.tokens[idx]), self.labels[idx]
         pad_mask = [0] * len(tokens) + [1] * len(labels)
         tokens = tokens + labels
+        if len(tokens) > self.seq_len + 1:
+            # longer than the model's window: keep the end of the passage (the target word is last)
+            # instead of failing to collate, which is all the reference does with such a sample
+            tokens, pad_mask = tokens[-(self.seq_len + 1):], pad_mask[-(self.seq_len + 1):]
         n = len(tokens)
         if n < self.seq_len + 1:
             pad_mask += [0] * (self.seq_len + 1 - n)

@@ -1,5 +1,7 @@
 """Downstream tasks on CPU: MNLI finetuning through tasks/main.py on a synthetic TSV, the
 zero-shot LM windowing, answer matching and F1."""
+import json
+import math
 import os
 import subprocess
 import sys
@@ -70,3 +72,52 @@ def test_mnli_finetune_cpu(tmp_path):
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "overall: correct / total = " in r.stdout and "done :-)" in r.stdout
+
+
+def _zeroshot(tmp_path, task, data, extra=()):
+    """tasks/main.py --task LAMBADA | WIKITEXT103 with a random tiny GPT on CPU."""
+    import random as _random
+    from tests.helpers.launch import free_port
+    words = ["alpha", "beta", "gamma", "delta", "kernel", "tensor", "memory", "stream", "token", "layer"]
+    chars = sorted(set("".join(words) + " .=\n"))
+    toks = [c if c != " " else "Ġ" for c in chars if c != "\n"] + ["Ċ", "<|endoftext|>"]
+    (tmp_path / "vocab.json").write_text(json.dumps({t: i for i, t in enumerate(toks)}))
+    (tmp_path / "merges.txt").write_text("#version: 0.2\n")
+    rng = _random.Random(0)
+    data(tmp_path, rng, words)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    cmd = [sys.executable, os.path.join(ROOT, "tasks", "main.py"), "--task", task,
+           "--valid_data", str(tmp_path / "eval_data"), "--tokenizer_type", "GPT2BPETokenizer",
+           "--vocab_file", str(tmp_path / "vocab.json"), "--merge_file", str(tmp_path / "merges.txt"),
+           "--num_layers", "2", "--hidden_size", "64", "--num_attention_heads", "4", "--seq_length", "64",
+           "--max_position_embeddings", "64", "--micro_batch_size", "4", "--log_interval", "100",
+           "--distributed_backend", "gloo", "--use_cpu_initialization", "--no_load_optim", "--no_load_rng",
+           "--num_workers", "0", *extra]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, cwd=ROOT, timeout=600)
+    assert r.returncode == 0, r.stdout[-2500:] + r.stderr[-2500:]
+    return r.stdout
+
+
+def test_zeroshot_wikitext_perplexity_cli(tmp_path):
+    def data(d, rng, words):
+        lines = [" = Heading = \n"] + [" ".join(rng.choice(words) for _ in range(40)) + " . \n" for _ in range(30)]
+        (d / "eval_data").write_text("".join(lines))
+    out = _zeroshot(tmp_path, "WIKITEXT103", data, ["--overlapping_eval", "32"])
+    import re
+    m = re.search(r"avg loss: ([0-9.E+-]+) \| ppl: ([0-9.E+-]+) \| adjusted ppl: ([0-9.E+-]+) \| token ratio: ([0-9.]+)", out)
+    assert m, out[-1500:]
+    loss, ppl = float(m.group(1)), float(m.group(2))
+    # an untrained model over a ~25-symbol vocabulary: loss near log(vocab), far from degenerate
+    assert 1.5 < loss < 6.0 and abs(ppl - math.exp(loss)) / ppl < 1e-2 and float(m.group(4)) > 1.0
+
+
+def test_zeroshot_lambada_accuracy_cli(tmp_path):
+    def data(d, rng, words):
+        rows = [{"text": " ".join(rng.choice(words) for _ in range(12))} for _ in range(10)]
+        (d / "eval_data").write_text("\n".join(json.dumps(r) for r in rows) + "\n")
+    out = _zeroshot(tmp_path, "LAMBADA", data)
+    import re
+    m = re.search(r"number correct: ([0-9.E+-]+) \| total examples: ([0-9.E+-]+) \| avg accuracy: ([0-9.E+-]+)", out)
+    assert m, out[-1500:]
+    assert float(m.group(2)) == 10 and 0.0 <= float(m.group(3)) <= 1.0

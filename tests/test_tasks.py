@@ -121,3 +121,40 @@ def test_zeroshot_lambada_accuracy_cli(tmp_path):
     m = re.search(r"number correct: ([0-9.E+-]+) \| total examples: ([0-9.E+-]+) \| avg accuracy: ([0-9.E+-]+)", out)
     assert m, out[-1500:]
     assert float(m.group(2)) == 10 and 0.0 <= float(m.group(3)) <= 1.0
+
+
+def test_race_finetune_cpu(tmp_path):
+    """RACE through tasks/main.py: multiple-choice head over NUM_CHOICES (context, question + option)
+    pairs per sample, one epoch of finetuning and the accuracy report."""
+    words = "the of and to in a is that for it as was with be by on not he this are".split()
+    vocab = ["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words
+    (tmp_path / "vocab.txt").write_text("\n".join(vocab) + "\n")
+    rng = np.random.RandomState(1)
+
+    def split(name, n_articles):
+        d = tmp_path / "RACE" / name / "middle"
+        d.mkdir(parents=True)
+        for a in range(n_articles):
+            doc = {"article": " ".join(rng.choice(words, 30)),
+                   "questions": [" ".join(rng.choice(words, 5)) + " ?", "it was _ by the"],
+                   "options": [[" ".join(rng.choice(words, 2)) for _ in range(4)] for _ in range(2)],
+                   "answers": ["ABCD"[int(rng.randint(4))] for _ in range(2)]}
+            (d / f"{a}.txt").write_text(json.dumps(doc) + "\n")
+        return str(d)
+    train, dev = split("train", 6), split("dev", 2)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1",
+               B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, os.path.join(ROOT, "tasks", "main.py"), "--task", "RACE", "--epochs", "1",
+           "--train_data", train, "--valid_data", dev,
+           "--tokenizer_type", "BertWordPieceLowerCase", "--vocab_file", str(tmp_path / "vocab.txt"),
+           "--num_layers", "2", "--hidden_size", "32", "--num_attention_heads", "2", "--seq_length", "64",
+           "--max_position_embeddings", "64", "--micro_batch_size", "2", "--global_batch_size", "2",
+           "--lr", "1e-3", "--lr_decay_style", "linear", "--lr_warmup_fraction", "0.1",
+           "--distributed_backend", "gloo", "--use_cpu_initialization", "--no_bias_gelu_fusion",
+           "--no_masked_softmax_fusion", "--num_workers", "0", "--log_interval", "2", "--eval_interval", "100",
+           "--eval_iters", "1", "--make_vocab_size_divisible_by", "8", "--hidden_dropout", "0.0",
+           "--attention_dropout", "0.0"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "total number of samples: 12" in r.stdout and "total number of samples: 4" in r.stdout
+    assert "overall: correct / total = " in r.stdout and "done :-)" in r.stdout

@@ -158,3 +158,54 @@ def test_race_finetune_cpu(tmp_path):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "total number of samples: 12" in r.stdout and "total number of samples: 4" in r.stdout
     assert "overall: correct / total = " in r.stdout and "done :-)" in r.stdout
+
+
+def test_msdp_preprocessing_and_f1(tmp_path):
+    """Wizard-of-Wikipedia dump -> tab-separated turns + reference files, response-stage input assembly,
+    prompt sampling, and the token-level F1 used to score both generation stages."""
+    wow = [{"chosen_topic": "Kernels", "dialog": [
+        {"speaker": "0_Apprentice", "text": "Tell me about\nGPU kernels."},
+        {"speaker": "1_Wizard", "text": "A kernel runs on many threads.",
+         "checked_sentence": {"s0": "A kernel is a function launched on the GPU."}, "checked_passage": {"p0": "CUDA"}},
+        {"speaker": "0_Apprentice", "text": "How many threads?"},
+        {"speaker": "1_Wizard", "text": "Thousands at once.", "checked_sentence": {}, "checked_passage": {}}]},
+        {"chosen_topic": "Memory", "dialog": [
+            {"speaker": "0_Wizard", "text": "Let us talk about memory."},
+            {"speaker": "1_Apprentice", "text": "Is HBM fast?"},
+            {"speaker": "0_Wizard", "text": "Yes, HBM3e delivers high bandwidth.",
+             "checked_sentence": {"s": "HBM3e delivers high bandwidth."}, "checked_passage": {}}]}]
+    raw = tmp_path / "wow.json"
+    raw.write_text(json.dumps(wow))
+    out, kref, rref = tmp_path / "proc.txt", tmp_path / "knwl_ref.txt", tmp_path / "resp_ref.txt"
+    pre = os.path.join(ROOT, "tasks", "msdp", "preprocessing.py")
+
+    def run(*a):
+        r = subprocess.run([sys.executable, pre, *map(str, a)], capture_output=True, text=True, cwd=ROOT, timeout=300)
+        assert r.returncode == 0, r.stderr[-2000:]
+    run("--func", "process_wow_dataset", "--raw_file", raw, "--processed_file", out, "--knwl_ref_file", kref,
+        "--resp_ref_file", rref)
+    rows = [l.rstrip("\n").split("\t") for l in open(out)]
+    assert rows == [["CUDA", "Tell me about GPU kernels.", "A kernel is a function launched on the GPU.",
+                     "A kernel runs on many threads."],
+                    ["Memory", "Let us talk about memory. [SEP] Is HBM fast?", "HBM3e delivers high bandwidth.",
+                     "Yes, HBM3e delivers high bandwidth."]]
+    assert open(kref).read().splitlines() == [r[2] for r in rows]
+    assert open(rref).read().splitlines() == [r[3] for r in rows]
+    gen = tmp_path / "knwl_gen.txt"
+    gen.write_text("A kernel is a GPU function.<|endoftext|>\nHBM is fast memory.\n")
+    resp_in = tmp_path / "resp_in.txt"
+    run("--func", "prepare_input", "--test_file", out, "--knwl_gen_file", gen, "--processed_file", resp_in)
+    got = [l.rstrip("\n").split("\t") for l in open(resp_in)]
+    assert [g[2] for g in got] == ["A kernel is a GPU function.", "HBM is fast memory."] and got[0][0] == "CUDA"
+    prompts = tmp_path / "resp_prompts.txt"
+    run("--func", "get_resp_gen_prompts", "--train_file", out, "--processed_file", prompts, "--seed", "7")
+    # only turns whose response re-uses most of the knowledge sentence qualify as prompts
+    assert open(prompts).read().splitlines() == [
+        "Topic: Memory. User says: Is HBM fast? We know that: HBM3e delivers high bandwidth. "
+        "System replies: Yes, HBM3e delivers high bandwidth."]
+    from msdp.metrics import F1Metric
+    p, r, f1 = F1Metric.compute_all_pairs(["The kernel is a GPU function!", "nothing in common"],
+                                          ["a kernel is a function launched on the gpu", "HBM3e delivers"])
+    # first pair: articles / punctuation dropped -> guess {kernel,is,gpu,function}, 4 of 4 in the answer
+    assert 0.4 < p < 0.6 and 0.25 < r < 0.45 and 0.3 < f1 < 0.5
+    assert F1Metric.compute_each_pair("same words here", "same words here")[2] == 1.0

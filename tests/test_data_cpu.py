@@ -193,3 +193,35 @@ def test_preprocess_and_merge_tools(tmp_path):
     both = ids.make_dataset(merged, "mmap", skip_warmup=True)
     assert len(both) == 6 and both.get_doc_idx().tolist() == [0, 1, 2, 3, 4, 5, 6]
     assert both[4].tolist() == ds[1].tolist()
+
+
+def test_retrieval_datastore_shards_and_mips_search(tmp_path):
+    """REALM / ORQA evidence store: per-rank shards are merged into one pickle, and the
+    maximum-inner-product index (FAISS when importable, dense torch otherwise) returns the blocks with
+    the largest dot products (megatron/data/realm_index.py:17-224 behaviour)."""
+    from epfl_megatron_b200.data.realm_index import FaissMIPSIndex, OpenRetreivalDataStore
+    rng = np.random.default_rng(3)
+    emb = rng.standard_normal((40, 16)).astype(np.float32)
+    path = str(tmp_path / "blocks.pkl")
+    for rank in range(2):                                 # two data-parallel ranks embed half each
+        store = OpenRetreivalDataStore(path, load_from_path=False, rank=rank)
+        ids = list(range(rank * 20, rank * 20 + 20))
+        store.add_block_data(ids, emb[ids])
+        with pytest.raises(ValueError):
+            store.add_block_data(ids[:1], emb[ids[:1]])
+        store.save_shard()
+    merged = OpenRetreivalDataStore(path, load_from_path=False, rank=0)
+    merged.merge_shards_and_save()
+    assert len(merged.embed_data) == 40 and not os.path.isdir(merged.temp_dir_name)
+    loaded = OpenRetreivalDataStore(path, load_from_path=True, rank=0)
+    assert sorted(loaded.embed_data) == list(range(40)) and loaded.embed_data[7].dtype == np.float16
+    index = FaissMIPSIndex(16, loaded)
+    assert loaded.embed_data == {}                         # handed over to the index
+    q = emb[[5, 31]] * 3.0
+    scores, ids = index.search_mips_index(torch.from_numpy(q), top_k=4, reconstruct=False)
+    want = np.argsort(-(q @ np.float32(np.float16(emb)).T), axis=1)[:, :4]
+    assert ids.shape == (2, 4) and np.array_equal(ids, want) and ids[0, 0] == 5 and ids[1, 0] == 31
+    assert np.all(np.diff(scores, axis=1) <= 1e-4)
+    blocks = index.search_mips_index(q, top_k=2, reconstruct=True)
+    got = blocks[-1] if isinstance(blocks, tuple) else blocks
+    assert np.asarray(got).shape == (2, 2, 16)

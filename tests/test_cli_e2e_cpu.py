@@ -66,3 +66,21 @@ def test_finetune_cli_train_eval_save_resume(tmp_path):
     its2 = [int(m) for m in re.findall(r"iteration\s+(\d+)/\s*9", out2)]
     assert its2 and its2[0] > 6 and its2[-1] <= 9
     assert open(tmp_path / "ckpt" / "latest_checkpointed_iteration.txt").read().strip() == "9"
+
+
+def test_sigterm_checkpoints_and_exits(tmp_path):
+    """--exit_signal_handler: a SIGTERM (here injected into rank 0 at iteration 3) makes the run save a
+    checkpoint at that iteration and stop; --exit_interval stops a run at a multiple of the interval
+    (megatron/training.py:712-748, dist_signal_handler.py)."""
+    from tests.helpers.launch import free_port
+    _corpus(str(tmp_path / "corpus"))
+    out = _finetune(tmp_path, free_port(), ["--train_iters", "9", "--exit_signal_handler",
+                                            "--fault_inject", "kill:0:3", "--save_interval", "100"])
+    assert "exiting program after receiving SIGTERM" in out, out[-1500:]
+    saved = open(tmp_path / "ckpt" / "latest_checkpointed_iteration.txt").read().strip()
+    assert saved in ("3", "4"), saved
+    assert not re.search(r"iteration\s+8/", out)
+    out2 = _finetune(tmp_path, free_port(), ["--train_iters", "9", "--load", str(tmp_path / "ckpt"),
+                                             "--exit_interval", "6", "--save_interval", "100"])
+    assert "exiting program at iteration 6" in out2, out2[-1500:]
+    assert open(tmp_path / "ckpt" / "latest_checkpointed_iteration.txt").read().strip() == "6"

@@ -433,6 +433,10 @@ class FlatOptimizer(MegatronOptimizer):
                        g["momentum"], wd, 1 if self.step_count == 1 else 0, self._coef.data_ptr(),
                        self._skip.data_ptr(), L.stream_ptr())
             return
+        # PyTorch path (CPU runs, kernels switched off): same contract as the kernels, which leave
+        # the segment untouched when the gradients of this step were not finite
+        if bool(self._skip.item()):
+            return
         gr = grad * self._coef
         if self.kind == "adam":
             ops_ref.adam_update(main, gr, m, v, lr, b1, b2, g["eps"], wd, self.step_count)

@@ -3,6 +3,7 @@ the command line (pretrain(): data iterators, train loop, periodic evaluation, l
 then a second invocation that resumes from the checkpoint and finishes the run.
 Reference: finetune.py:141-150 -> megatron/training.py:54-167, :639-807, :855-939."""
 import json
+import math
 import os
 import re
 import subprocess
@@ -84,3 +85,15 @@ def test_sigterm_checkpoints_and_exits(tmp_path):
                                              "--exit_interval", "6", "--save_interval", "100"])
     assert "exiting program at iteration 6" in out2, out2[-1500:]
     assert open(tmp_path / "ckpt" / "latest_checkpointed_iteration.txt").read().strip() == "6"
+
+
+def test_non_finite_gradient_skips_the_update(tmp_path):
+    """A NaN planted in one gradient (--fault_inject nan:<rank>:<iteration>): the step's gradient norm
+    is reported as nan, the parameters are left untouched by that step, and training carries on with
+    finite losses afterwards."""
+    from tests.helpers.launch import free_port
+    _corpus(str(tmp_path / "corpus"))
+    out = _finetune(tmp_path, free_port(), ["--train_iters", "6", "--fault_inject", "nan:0:2", "--log_interval", "1"])
+    losses = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+|nan)", out)]
+    assert len(losses) == 6 and all(math.isfinite(x) for x in losses), out[-2500:]
+    assert re.search(r"iteration\s+3/.*grad norm: nan", out), out[-2500:]

@@ -97,3 +97,31 @@ def test_non_finite_gradient_skips_the_update(tmp_path):
     losses = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+|nan)", out)]
     assert len(losses) == 6 and all(math.isfinite(x) for x in losses), out[-2500:]
     assert re.search(r"iteration\s+3/.*grad norm: nan", out), out[-2500:]
+
+
+def test_pretrain_gpt_sample_based_with_batch_rampup(tmp_path):
+    """pretrain_gpt.py (GPT-2 style: LayerNorm, GeLU, learned absolute positions, tied embeddings),
+    sample-based schedule (--train_samples / --lr_decay_samples / --lr_warmup_samples) with a global
+    batch size that ramps 2 -> 4 -> 6 (megatron/microbatches.py:78-144)."""
+    from tests.helpers.launch import free_port
+    _corpus(str(tmp_path / "corpus"))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    cmd = [sys.executable, os.path.join(ROOT, "pretrain_gpt.py"),
+           "--num_layers", "2", "--hidden_size", "64", "--num_attention_heads", "4", "--seq_length", "32",
+           "--max_position_embeddings", "32", "--micro_batch_size", "2", "--global_batch_size", "6",
+           "--rampup_batch_size", "2", "2", "24", "--train_samples", "60", "--lr_decay_samples", "60",
+           "--lr_warmup_samples", "8", "--lr", "1e-3", "--min_lr", "1e-4", "--lr_decay_style", "linear",
+           "--tokenizer_type", "NullTokenizer", "--vocab_size", "1024", "--data_path", str(tmp_path / "corpus"),
+           "--split", "90,5,5", "--distributed_backend", "gloo", "--log_interval", "1", "--eval_interval", "1000",
+           "--eval_iters", "1", "--num_workers", "0", "--use_cpu_initialization", "--no_bias_gelu_fusion",
+           "--no_masked_softmax_fusion", "--hidden_dropout", "0", "--attention_dropout", "0"]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, cwd=ROOT, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    gbs = [int(x) for x in re.findall(r"global batch size:\s+(\d+)", r.stdout)]
+    consumed = [int(x) for x in re.findall(r"consumed samples:\s+(\d+)", r.stdout)]
+    assert gbs[0] == 2 and gbs[-1] == 6 and sorted(set(gbs)) == [2, 4, 6] and gbs == sorted(gbs), gbs
+    assert consumed[-1] >= 60 and all(b - a == g for a, b, g in zip(consumed, consumed[1:], gbs[1:])), (consumed, gbs)
+    losses = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", r.stdout)]
+    # uniformly random tokens: nothing to learn beyond log(vocab) ~ 6.9, but it must stay there
+    assert len(losses) == len(gbs) and all(6.0 < x < 8.0 for x in losses), losses

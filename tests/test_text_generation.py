@@ -63,3 +63,50 @@ def test_generation_end_to_end_cpu():
     for k in ("greedy_matches_uncached", "logprobs_finite", "sampled_texts", "score_shape_ok", "beam_ok",
               "server_ok", "server_rejects", "server_beam"):
         assert out[k], (k, out)
+
+
+def test_server_cli_tensor_parallel_and_client(tmp_path):
+    """tools/run_text_generation_server.py under torchrun with two tensor-parallel ranks: rank 0 serves
+    HTTP, rank 1 sits in the worker loop and is driven by the broadcast opcodes; queried through the
+    interactive client tools/text_generation_cli.py (megatron/text_generation_server.py:22-29,
+    tools/run_text_generation_server.py:49-84)."""
+    import socket
+    import time
+    port = free_port()
+    env = dict(os.environ, B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", str(free_port()), os.path.join(ROOT, "tools", "run_text_generation_server.py"),
+           "--model_name", "llama2", "--tensor_model_parallel_size", "2", "--num_layers", "2", "--hidden_size", "64",
+           "--num_attention_heads", "4", "--num_attention_heads_kv", "2", "--ffn_hidden_size", "128",
+           "--seq_length", "64", "--max_position_embeddings", "64", "--micro_batch_size", "1", "--use_rms_norm",
+           "--glu_activation", "swiglu", "--no_tie_embed_logits", "--position_embedding_type", "rotary",
+           "--no_bias_gelu_fusion", "--tokenizer_type", "NullTokenizer", "--vocab_size", "512",
+           "--distributed_backend", "gloo", "--use_cpu_initialization", "--host", "127.0.0.1", "--port", str(port)]
+    log = open(tmp_path / "server.log", "w")
+    server = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, env=env, cwd=ROOT)
+    try:
+        deadline = time.time() + 180
+        while time.time() < deadline:
+            assert server.poll() is None, open(tmp_path / "server.log").read()[-3000:]
+            try:
+                socket.create_connection(("127.0.0.1", port), timeout=1).close()
+                break
+            except OSError:
+                time.sleep(1)
+        else:
+            raise AssertionError("server did not come up:\n" + open(tmp_path / "server.log").read()[-3000:])
+        client = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "text_generation_cli.py"),
+                                 f"127.0.0.1:{port}"], input="5 6 7 8\n6\n9 10\n3\n", capture_output=True, text=True,
+                                timeout=300, cwd=ROOT)
+        assert client.returncode == 0, client.stderr[-2000:]
+        answers = [ln for ln in client.stdout.splitlines() if ln and ln[0].isdigit()]
+        assert len(answers) == 2, client.stdout
+        first, second = answers[0].split(), answers[1].split()
+        assert first[:4] == ["5", "6", "7", "8"] and len(first) == 10 and second[:2] == ["9", "10"] and len(second) == 5
+    finally:
+        server.terminate()
+        try:
+            server.wait(timeout=30)
+        except subprocess.TimeoutExpired:
+            server.kill()
+        log.close()

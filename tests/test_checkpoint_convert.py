@@ -289,3 +289,40 @@ def test_meta_llama_to_hf_cli(tmp_path):
     for k, v in sd.items():
         assert torch.equal(got[k], v), k
     assert back.config.num_key_value_heads == 2 and back.config.intermediate_size == 96
+
+
+def test_verify_correctness_cli(tmp_path):
+    """verify_correctness.py as a user runs it: a converted Megatron checkpoint against the HF model it
+    came from, on batches drawn from a tokenised corpus; reports max / mean absolute logit error per batch
+    and the loss difference (reference: verify_correctness.py:107-166, gate 1e-3 in tests/test_llama_weights.py)."""
+    import re
+    import numpy as np
+    import weights2megatron as w2m
+    from epfl_megatron_b200.data import indexed_dataset as ids
+    from tests.helpers.launch import free_port
+    hf, cfg = _tiny_hf_llama(2)
+    hf.save_pretrained(tmp_path / "hf")
+    w2m.convert("llama2", 7, tmp_path / "mega", dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    rng = np.random.default_rng(0)
+    b = ids.MMapIndexedDatasetBuilder(ids.data_file_path(str(tmp_path / "corpus")), dtype=np.uint16)
+    for _ in range(100):
+        b.add_item(torch.tensor(rng.integers(1, 250, size=int(rng.integers(30, 120)))))
+        b.end_document()
+    b.finalize(ids.index_file_path(str(tmp_path / "corpus")))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    cmd = [sys.executable, os.path.join(ROOT, "verify_correctness.py"), "--model_name", "llama2",
+           "--load", str(tmp_path / "mega"), "--data_path", str(tmp_path / "corpus"), "--split", "100,0,0",
+           "--tokenizer_type", "NullTokenizer", "--vocab_size", "256", "--make_vocab_size_divisible_by", "1",
+           "--huggingface_cache", str(tmp_path / "hf"), "--verify_batches", "3", "--distributed_backend", "gloo",
+           "--use_cpu_initialization", "--no_load_optim", "--no_load_rng", "--num_workers", "0", "--eval_iters", "0"]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, cwd=ROOT, timeout=600)
+    assert r.returncode == 0, r.stdout[-2500:] + r.stderr[-2500:]
+    maxima = [float(x) for x in re.findall(r"Max absoulute error in the logits: max=([0-9.]+)", r.stdout)]
+    assert len(maxima) == 3 and max(maxima) <= 1e-3, r.stdout[-1500:]
+    mean = float(re.search(r"Mean of the per-batch max abs logit errors: ([0-9.]+)", r.stdout).group(1))
+    assert mean <= 1e-3
+    diffs = [float(x) for x in re.findall(r"Abs loss error: ([0-9.]+)", r.stdout)]
+    # the HF side scores positions 0..s-2 of the same tokens (labels shifted inside the model), this
+    # side all s positions against the data's labels: equal logits, slightly different mean loss
+    assert len(diffs) == 3 and max(diffs) <= 2e-2

@@ -281,9 +281,15 @@ def test_meta_llama_to_hf_cli(tmp_path):
         torch.save(shard, src / f"consolidated.{r:02d}.pth")
     (src / "params.json").write_text(json.dumps({"dim": 64, "n_layers": 2, "n_heads": 4, "n_kv_heads": 2,
                                                  "norm_eps": 1e-5, "vocab_size": -1}))
+    spm = pytest.importorskip("sentencepiece")
+    (tmp_path / "c.txt").write_text("\n".join(["the quick brown fox jumps over the lazy dog"] * 60))
+    spm.SentencePieceTrainer.train(input=str(tmp_path / "c.txt"), model_prefix=str(src / "tokenizer"), vocab_size=40,
+                                   model_type="bpe", bos_id=1, eos_id=2, unk_id=0, pad_id=-1)
     out = tmp_path / "hf_out"
     _run(["weights2megatron/convert_llama2hf.py", "--input_dir", str(src), "--model_size", "13",
           "--output_dir", str(out)])
+    tok = transformers.AutoTokenizer.from_pretrained(str(out))
+    assert len(tok) == 40 and len(tok("the quick fox")["input_ids"]) >= 3
     back = transformers.LlamaForCausalLM.from_pretrained(str(out), torch_dtype=torch.float32)
     got = back.state_dict()
     for k, v in sd.items():
@@ -326,3 +332,38 @@ def test_verify_correctness_cli(tmp_path):
     # the HF side scores positions 0..s-2 of the same tokens (labels shifted inside the model), this
     # side all s positions against the data's labels: equal logits, slightly different mean loss
     assert len(diffs) == 3 and max(diffs) <= 2e-2
+
+
+def test_megatron2hf_cli_with_tokenizer(tmp_path):
+    """weights2megatron/megatron2hf.py from the command line: the exported HF directory loads with
+    transformers, reproduces the source weights, and carries a tokenizer whose added special tokens sit
+    at the ids the Megatron SentencePiece tokenizer gave them."""
+    spm = pytest.importorskip("sentencepiece")
+    transformers = pytest.importorskip("transformers")
+    import weights2megatron as w2m
+    hf, cfg = _tiny_hf_llama(2)
+    mega = tmp_path / "mega"
+    w2m.convert("llama2", 7, mega, dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    corpus = tmp_path / "c.txt"
+    corpus.write_text("\n".join(["the quick brown fox jumps over the lazy dog", "pack my box with five dozen jugs"] * 40))
+    spm.SentencePieceTrainer.train(input=str(corpus), model_prefix=str(tmp_path / "tok"), vocab_size=60,
+                                   model_type="bpe", bos_id=1, eos_id=2, unk_id=0, pad_id=-1)
+    # the release checkpoint's args name the tokenizer that was used for training
+    ck = mega / "release" / "mp_rank_00" / "model_optim_rng.pt"
+    sd = torch.load(ck, weights_only=False)
+    sd["args"].tokenizer_type, sd["args"].vocab_extra_ids, sd["args"].vocab_extra_ids_list = "SentencePieceTokenizer", 0, None
+    sd["args"].new_tokens = True
+    torch.save(sd, ck)
+    out = tmp_path / "hf_out"
+    _run(["weights2megatron/megatron2hf.py", "--model", "llama2", "--input_dir", str(mega), "--output_dir", str(out),
+          "--vocab_file", str(tmp_path / "tok.model"), "--dtype", "fp32"])
+    back = transformers.LlamaForCausalLM.from_pretrained(str(out), torch_dtype=torch.float32)
+    for k, v in hf.state_dict().items():
+        if "rotary" not in k:
+            assert torch.equal(back.state_dict()[k], v), k
+    tok = transformers.AutoTokenizer.from_pretrained(str(out))
+    from epfl_megatron_b200.tokenizer.tokenizer import _SentencePieceTokenizer
+    mt = _SentencePieceTokenizer(str(tmp_path / "tok.model"), new_tokens=True)
+    for name in ("<CLS>", "<SEP>", "<EOD>", "<MASK>"):
+        assert tok.convert_tokens_to_ids(name) == mt.vocab[name], name
+    assert len(tok) == mt.vocab_size

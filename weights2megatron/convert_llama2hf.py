@@ -63,9 +63,11 @@ def write_model(model_path, input_base_path, model_size, safe_serialization=True
 def write_tokenizer(tokenizer_path, input_tokenizer_path):
     os.makedirs(tokenizer_path, exist_ok=True)
     try:
-        from transformers import LlamaTokenizerFast
-        LlamaTokenizerFast(str(input_tokenizer_path)).save_pretrained(tokenizer_path)
-    except Exception:  # noqa: BLE001 - without the fast tokenizer stack keep the sentencepiece model
+        from megatron2hf import load_sentencepiece_as_hf
+        tok = load_sentencepiece_as_hf(str(input_tokenizer_path))
+        assert len(tok) >= 10
+        tok.save_pretrained(tokenizer_path)
+    except Exception:  # noqa: BLE001 - without the HF tokenizer stack keep the sentencepiece model
         shutil.copy(input_tokenizer_path, os.path.join(tokenizer_path, "tokenizer.model"))
 
 

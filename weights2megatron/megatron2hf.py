@@ -142,6 +142,24 @@ def write_falcon_model(model_path, input_dir, dtype=torch.bfloat16, safe=True):
     return model
 
 
+def load_sentencepiece_as_hf(vocab_file):
+    """HF Llama tokenizer over a SentencePiece model file. transformers 5 reads the model only through
+    ``from_pretrained`` on a directory holding ``tokenizer.model`` (its constructor's first arguments became
+    vocab / merges); transformers 4 took ``vocab_file=`` directly."""
+    import shutil
+    import tempfile
+    from transformers import LlamaTokenizer
+    with tempfile.TemporaryDirectory() as d:
+        shutil.copy(vocab_file, os.path.join(d, "tokenizer.model"))
+        try:
+            tok = LlamaTokenizer.from_pretrained(d)
+        except Exception:  # noqa: BLE001
+            tok = None
+    if tok is None or len(tok) < 10:
+        tok = LlamaTokenizer(vocab_file=vocab_file)
+    return tok
+
+
 def write_tokenizer(args, model_path, vocab_file=None, override_special_tokens=None):
     """Save the tokenizer next to the model; Megatron's extra special tokens are added and the
     ids are checked against the Megatron tokenizer."""
@@ -150,8 +168,7 @@ def write_tokenizer(args, model_path, vocab_file=None, override_special_tokens=N
         from transformers import AutoTokenizer
         tok = AutoTokenizer.from_pretrained(vocab_file or "tiiuae/falcon-40b")
     elif tt == "SentencePieceTokenizer" and vocab_file:
-        from transformers import LlamaTokenizer
-        tok = LlamaTokenizer(vocab_file=vocab_file)
+        tok = load_sentencepiece_as_hf(vocab_file)
         from epfl_megatron_b200.tokenizer.tokenizer import _SentencePieceTokenizer
         mt = _SentencePieceTokenizer(vocab_file, vocab_extra_ids=getattr(args, "vocab_extra_ids", 0),
                                      vocab_extra_ids_list=getattr(args, "vocab_extra_ids_list", None),

@@ -367,3 +367,33 @@ def test_megatron2hf_cli_with_tokenizer(tmp_path):
     for name in ("<CLS>", "<SEP>", "<EOD>", "<MASK>"):
         assert tok.convert_tokens_to_ids(name) == mt.vocab[name], name
     assert len(tok) == mt.vocab_size
+
+
+def test_weights2megatron_cli_reads_dimensions_from_the_source(tmp_path):
+    """weights2megatron.py from the command line on a HF directory of a non-standard size: the model
+    dimensions come from its config.json (the built-in size table only knows the published checkpoints),
+    and the release checkpoint equals the in-memory conversion."""
+    import weights2megatron as w2m
+    hf, cfg = _tiny_hf_llama(2)
+    hf.save_pretrained(tmp_path / "hf")
+    _run(["weights2megatron/weights2megatron.py", "llama2", "--size", "7", "--out", str(tmp_path / "cli"),
+          "--model_path", str(tmp_path / "hf"), "--dtype", "fp32"])
+    w2m.convert("llama2", 7, tmp_path / "api", dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    a = torch.load(tmp_path / "cli" / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
+    b = torch.load(tmp_path / "api" / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
+    assert (tmp_path / "cli" / "latest_checkpointed_iteration.txt").read_text() == "release"
+    for k in ("num_layers", "hidden_size", "num_attention_heads", "num_attention_heads_kv", "ffn_hidden_size",
+              "max_position_embeddings", "padded_vocab_size"):
+        assert getattr(a["args"], k) == getattr(b["args"], k), k
+    assert a["args"].num_layers == 4 and a["args"].ffn_hidden_size == 176
+
+    def flat(d, prefix=""):
+        for k, v in d.items():
+            if isinstance(v, dict):
+                yield from flat(v, prefix + k + ".")
+            else:
+                yield prefix + k, v
+    fa, fb = dict(flat(a["model"]["language_model"])), dict(flat(b["model"]["language_model"]))
+    assert fa.keys() == fb.keys()
+    for k in fa:
+        assert torch.equal(fa[k], fb[k]), k

@@ -125,6 +125,20 @@ def convert(model, size, out, model_path=None, cache_dir=None, dtype=torch.bfloa
         if state_dict is None:
             weights, source = merge_llama(size, version, cache_dir, model_path)
             n_layer, hidden, n_heads, n_kv, ffn = LLAMA_SIZES[size]
+            # the size table covers the published checkpoints; when the source directory describes
+            # itself (HF config.json, Meta params.json) its numbers win, so any Llama-shaped model converts
+            src = Path(model_path or cache_dir or ".")
+            if source == "hf" and (src / "config.json").exists():
+                from transformers import AutoConfig
+                config = AutoConfig.from_pretrained(src)
+                n_layer, hidden, n_heads = config.num_hidden_layers, config.hidden_size, config.num_attention_heads
+                n_kv, ffn = config.num_key_value_heads, config.intermediate_size
+            elif source == "meta" and (src / "params.json").exists():
+                import json
+                params = json.loads((src / "params.json").read_text())
+                n_layer, hidden, n_heads = params["n_layers"], params["dim"], params["n_heads"]
+                n_kv = params.get("n_kv_heads", n_heads)
+                ffn = weights["layers.0.feed_forward.w1.weight"].shape[0]
         else:
             weights, source = hf_state_to_meta(state_dict), "hf"
             n_layer, hidden, n_heads = config.num_hidden_layers, config.hidden_size, config.num_attention_heads

@@ -397,3 +397,29 @@ def test_weights2megatron_cli_reads_dimensions_from_the_source(tmp_path):
     assert fa.keys() == fb.keys()
     for k in fa:
         assert torch.equal(fa[k], fb[k]), k
+
+
+def test_permute_qkv_migration_cli(tmp_path):
+    """weights2megatron/permute_qkv.py: a checkpoint whose fused QKV rows were left in HF's half-rotation
+    order (converted without the permutation) becomes identical to a correctly converted one."""
+    import weights2megatron as w2m
+    hf, cfg = _tiny_hf_llama(2)
+    good = tmp_path / "good"
+    w2m.convert("llama2", 7, good, dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    # the faulty conversion: same pipeline, but the q/k rows are taken as if they were already interleaved
+    import merge_llama as ml
+    lm = w2m.llama_to_megatron(ml.hf_state_to_meta(hf.state_dict()), 4, 64, 4, 2, source="meta")
+    ck = torch.load(good / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
+    bad = tmp_path / "bad"
+    w2m.save_release(lm, ck["args"], bad, torch.float32)
+    fixed = tmp_path / "fixed"
+    _run(["weights2megatron/permute_qkv.py", "--input_dir", str(bad), "--output_dir", str(fixed)])
+    a = torch.load(fixed / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
+    ea, eg = a["model"]["language_model"]["encoder"], ck["model"]["language_model"]["encoder"]
+    bad_enc = torch.load(bad / "release" / "mp_rank_00" / "model_optim_rng.pt",
+                         weights_only=False)["model"]["language_model"]["encoder"]
+    key = "layers.0.self_attention.query_key_value.weight"
+    assert not torch.equal(bad_enc[key], eg[key])
+    for k in eg:
+        assert torch.equal(ea[k], eg[k]), k
+    assert (fixed / "latest_checkpointed_iteration.txt").read_text() == "release"

@@ -30,10 +30,9 @@ def update_checkpoint(input_dir: Path, output_dir: Path, overwrite_ok: bool = Fa
         tp = getattr(a, "tensor_model_parallel_size", 1)
         for k in list(enc):
             if re.match(r"^layers\.[0-9]+\.(self_)?attention\.query_key_value\.weight$", k):
-                enc[k] = permute_qkv(enc[k], a.hidden_size // 1, a.num_attention_heads // tp,
-                                     a.num_attention_heads_kv // tp) if False else \
-                    permute_qkv(enc[k], (a.hidden_size // a.num_attention_heads) * (a.num_attention_heads // tp),
-                                a.num_attention_heads // tp, a.num_attention_heads_kv // tp)
+                # a tensor-parallel shard holds whole KV groups: local head counts, same head size
+                heads, kv = a.num_attention_heads // tp, a.num_attention_heads_kv // tp
+                enc[k] = permute_qkv(enc[k], (a.hidden_size // a.num_attention_heads) * heads, heads, kv)
         out.parent.mkdir(parents=True, exist_ok=True)
         torch.save(sd, out)
     (output_dir / "latest_checkpointed_iteration.txt").write_text(it)

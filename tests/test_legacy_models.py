@@ -32,3 +32,34 @@ def test_legacy_model_trains(mode, keys, tmp_path):
     losses = out["losses"]
     assert all(x == x and x < 50 for x in losses)
     assert min(losses[3:]) < losses[0], losses
+
+
+@pytest.mark.parametrize("script,extra", [
+    ("pretrain_bert.py", ""),
+    ("pretrain_t5.py", "--decoder_seq_length 32 --vocab_extra_ids 100 --kv_channels 16 --ffn_hidden_size 128"),
+    ("pretrain_ict.py", "--titles_data_path {titles} --query_in_block_prob 0.2 --ict_head_size 32 "
+                        "--biencoder_projection_dim 32 --retriever_report_topk_accuracies 1 2 --retriever_score_scaling"),
+])
+def test_legacy_entry_points_from_the_command_line(script, extra, tmp_path):
+    """The three legacy entry points as a user starts them: pretrain() with evaluation, logging and a
+    checkpoint at the end."""
+    sys.path.insert(0, os.path.join(ROOT, "tests", "helpers"))
+    try:
+        import legacy_worker
+    finally:
+        sys.path.pop(0)
+    vf, prefix, titles = legacy_worker.make_corpus(str(tmp_path))
+    argv = (f"--num_layers 2 --hidden_size 64 --num_attention_heads 4 --seq_length 48 --max_position_embeddings 64 "
+            f"--micro_batch_size 4 --global_batch_size 4 --train_iters 4 --lr 2e-3 --min_lr 1e-4 "
+            f"--lr_decay_style constant --tokenizer_type BertWordPieceLowerCase --vocab_file {vf} --data_path {prefix} "
+            f"--split 90,5,5 --distributed_backend gloo --use_cpu_initialization --hidden_dropout 0.0 "
+            f"--attention_dropout 0.0 --no_bias_gelu_fusion --no_masked_softmax_fusion --num_workers 0 "
+            f"--eval_iters 1 --eval_interval 2 --log_interval 2 --make_vocab_size_divisible_by 8 --data_impl mmap "
+            f"--seed 7 --save {tmp_path / 'ckpt'} --save_interval 4 " + extra.format(titles=titles)).split()
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1",
+               LOCAL_RANK="0", B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, script)] + argv, capture_output=True, text=True,
+                       timeout=900, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2500:] + r.stderr[-3500:]
+    assert "iteration        4/       4" in r.stdout and "validation loss at iteration 2" in r.stdout, r.stdout[-2000:]
+    assert open(tmp_path / "ckpt" / "latest_checkpointed_iteration.txt").read().strip() == "4"

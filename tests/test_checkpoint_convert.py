@@ -423,3 +423,30 @@ def test_permute_qkv_migration_cli(tmp_path):
     for k in eg:
         assert torch.equal(ea[k], eg[k]), k
     assert (fixed / "latest_checkpointed_iteration.txt").read_text() == "release"
+
+
+@pytest.mark.parametrize("new_arch", [True, False])
+def test_falcon_cli_both_architectures(tmp_path, new_arch):
+    """Falcon through the command lines in both directions: HF directory -> weights2megatron.py ->
+    megatron2hf.py -> HF directory with identical weights and logits; the 40B-style block (grouped KV heads,
+    two LayerNorms) and the 7B-style block (one KV head, one LayerNorm)."""
+    from transformers import FalconConfig, FalconForCausalLM
+    torch.manual_seed(2)
+    cfg = FalconConfig(vocab_size=128, hidden_size=64, num_hidden_layers=2, num_attention_heads=4,
+                       num_kv_heads=2 if new_arch else 1, multi_query=not new_arch,
+                       new_decoder_architecture=new_arch, parallel_attn=True, bias=False, alibi=False)
+    hf = FalconForCausalLM(cfg).float().eval()
+    hf.save_pretrained(tmp_path / "hf")
+    _run(["weights2megatron/weights2megatron.py", "falcon", "--size", "40" if new_arch else "7",
+          "--out", str(tmp_path / "mega"), "--model_path", str(tmp_path / "hf"), "--dtype", "fp32"])
+    ck = torch.load(tmp_path / "mega" / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
+    assert ck["args"].parallel_layernorm == new_arch and ck["args"].num_attention_heads_kv == (2 if new_arch else 1)
+    _run(["weights2megatron/megatron2hf.py", "--model", "falcon", "--input_dir", str(tmp_path / "mega"),
+          "--output_dir", str(tmp_path / "back"), "--dtype", "fp32"])
+    back = FalconForCausalLM.from_pretrained(str(tmp_path / "back"), torch_dtype=torch.float32).eval()
+    ref = hf.state_dict()
+    for k, v in back.state_dict().items():
+        assert torch.equal(v, ref[k]), k
+    ids = torch.randint(0, 128, (2, 24))
+    with torch.no_grad():
+        assert torch.equal(back(ids).logits, hf(ids).logits)

@@ -205,7 +205,12 @@ def main():
     else:
         write_llama_model(a.output_dir, a.input_dir, a.true_vocab_size, dt)
     _, margs = load_megatron(a.input_dir)
-    write_tokenizer(margs, a.output_dir, a.vocab_file, a.override_special_tokens)
+    try:
+        write_tokenizer(margs, a.output_dir, a.vocab_file, a.override_special_tokens)
+    except OSError as e:
+        # e.g. the Falcon tokenizer lives on the hub and this machine is offline: the weights are
+        # exported, the tokenizer can be added later (--vocab_file <local tokenizer directory>)
+        print(f"WARNING: model written, tokenizer NOT written ({type(e).__name__}: {str(e).splitlines()[0]})")
 
 
 if __name__ == "__main__":

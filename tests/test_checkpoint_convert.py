@@ -450,3 +450,35 @@ def test_falcon_cli_both_architectures(tmp_path, new_arch):
     ids = torch.randint(0, 128, (2, 24))
     with torch.no_grad():
         assert torch.equal(back(ids).logits, hf(ids).logits)
+
+
+def test_reshard_repads_the_vocabulary(tmp_path):
+    """checkpoint_util --true_vocab_size: rows beyond the real vocabulary are dropped and the table is
+    padded again (with copies of the last real row) for the target tensor-parallel size (multiple of make_vocab_size_divisible_by x tp), in
+    the embedding and the untied LM head alike (tools/checkpoint_saver_megatron.py:190-226)."""
+    import weights2megatron as w2m
+    hf, cfg = _tiny_hf_llama(2)                       # vocab 256
+    mega = tmp_path / "mega"
+    w2m.convert("llama2", 7, mega, dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    ck = mega / "release" / "mp_rank_00" / "model_optim_rng.pt"
+    sd = torch.load(ck, weights_only=False)
+    sd["args"].make_vocab_size_divisible_by = 64
+    torch.save(sd, ck)
+    out = tmp_path / "tp2"
+    _run(["tools/checkpoint_util.py", "--model_type", "llama2", "--load_dir", str(mega), "--save_dir", str(out),
+          "--target_tensor_parallel_size", "2", "--target_pipeline_parallel_size", "1", "--true_vocab_size", "200"])
+    shards = [torch.load(out / "release" / f"mp_rank_0{t}" / "model_optim_rng.pt", weights_only=False) for t in range(2)]
+    assert shards[0]["args"].padded_vocab_size == 256 and shards[0]["args"].tensor_model_parallel_size == 2
+    emb = torch.cat([s["model"]["language_model"]["embedding"]["word_embeddings"]["weight"] for s in shards])
+    head = torch.cat([s["model"]["language_model"]["lm_head"] for s in shards])
+    ref_e, ref_h = hf.state_dict()["model.embed_tokens.weight"], hf.state_dict()["lm_head.weight"]
+    assert emb.shape == (256, 64) and torch.equal(emb[:200], ref_e[:200]) and torch.equal(head[:200], ref_h[:200])
+    # the padding rows replicate the last real row, as the reference's saver does
+    assert torch.equal(emb[200:], ref_e[199:200].expand(56, -1)) and torch.equal(head[200:], ref_h[199:200].expand(56, -1))
+    # a target that needs a larger table: 200 real rows -> multiple of 64 x 4
+    out4 = tmp_path / "tp4"
+    _run(["tools/checkpoint_util.py", "--model_type", "llama2", "--load_dir", str(mega), "--save_dir", str(out4),
+          "--target_tensor_parallel_size", "4", "--target_pipeline_parallel_size", "1", "--true_vocab_size", "200"])
+    s0 = torch.load(out4 / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
+    assert s0["args"].padded_vocab_size == 256
+    assert s0["model"]["language_model"]["embedding"]["word_embeddings"]["weight"].shape == (64, 64)

@@ -457,7 +457,7 @@ def test_reshard_repads_the_vocabulary(tmp_path):
     padded again (with copies of the last real row) for the target tensor-parallel size (multiple of make_vocab_size_divisible_by x tp), in
     the embedding and the untied LM head alike (tools/checkpoint_saver_megatron.py:190-226)."""
     import weights2megatron as w2m
-    hf, cfg = _tiny_hf_llama(2)                       # vocab 256
+    hf, cfg = _tiny_hf_llama(4)                       # vocab 256, 4 KV heads (shardable 4 ways)
     mega = tmp_path / "mega"
     w2m.convert("llama2", 7, mega, dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
     ck = mega / "release" / "mp_rank_00" / "model_optim_rng.pt"

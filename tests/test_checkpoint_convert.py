@@ -24,7 +24,9 @@ def _tiny_hf_llama(kv_heads=2):
 
 
 def _run(cmd):
-    r = subprocess.run([sys.executable] + cmd, capture_output=True, text=True, cwd=ROOT)
+    # offline box: make hub look-ups fail at once instead of after connection retries
+    env = dict(os.environ, HF_HUB_OFFLINE="1", TRANSFORMERS_OFFLINE="1")
+    r = subprocess.run([sys.executable] + cmd, capture_output=True, text=True, cwd=ROOT, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     return r
 
@@ -425,22 +427,20 @@ def test_permute_qkv_migration_cli(tmp_path):
     assert (fixed / "latest_checkpointed_iteration.txt").read_text() == "release"
 
 
-@pytest.mark.parametrize("new_arch", [True, False])
-def test_falcon_cli_both_architectures(tmp_path, new_arch):
+def test_falcon_cli_round_trip(tmp_path):
     """Falcon through the command lines in both directions: HF directory -> weights2megatron.py ->
-    megatron2hf.py -> HF directory with identical weights and logits; the 40B-style block (grouped KV heads,
-    two LayerNorms) and the 7B-style block (one KV head, one LayerNorm)."""
+    megatron2hf.py -> HF directory with identical weights and logits (40B-style block: grouped KV heads,
+    two LayerNorms)."""
     from transformers import FalconConfig, FalconForCausalLM
     torch.manual_seed(2)
-    cfg = FalconConfig(vocab_size=128, hidden_size=64, num_hidden_layers=2, num_attention_heads=4,
-                       num_kv_heads=2 if new_arch else 1, multi_query=not new_arch,
-                       new_decoder_architecture=new_arch, parallel_attn=True, bias=False, alibi=False)
+    cfg = FalconConfig(vocab_size=128, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, num_kv_heads=2,
+                       new_decoder_architecture=True, parallel_attn=True, bias=False, alibi=False)
     hf = FalconForCausalLM(cfg).float().eval()
     hf.save_pretrained(tmp_path / "hf")
-    _run(["weights2megatron/weights2megatron.py", "falcon", "--size", "40" if new_arch else "7",
-          "--out", str(tmp_path / "mega"), "--model_path", str(tmp_path / "hf"), "--dtype", "fp32"])
+    _run(["weights2megatron/weights2megatron.py", "falcon", "--size", "40", "--out", str(tmp_path / "mega"),
+          "--model_path", str(tmp_path / "hf"), "--dtype", "fp32"])
     ck = torch.load(tmp_path / "mega" / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
-    assert ck["args"].parallel_layernorm == new_arch and ck["args"].num_attention_heads_kv == (2 if new_arch else 1)
+    assert ck["args"].parallel_layernorm and ck["args"].num_attention_heads_kv == 2
     _run(["weights2megatron/megatron2hf.py", "--model", "falcon", "--input_dir", str(tmp_path / "mega"),
           "--output_dir", str(tmp_path / "back"), "--dtype", "fp32"])
     back = FalconForCausalLM.from_pretrained(str(tmp_path / "back"), torch_dtype=torch.float32).eval()
@@ -450,6 +450,23 @@ def test_falcon_cli_both_architectures(tmp_path, new_arch):
     ids = torch.randint(0, 128, (2, 24))
     with torch.no_grad():
         assert torch.equal(back(ids).logits, hf(ids).logits)
+
+
+def test_falcon_multi_query_block_round_trip(tmp_path):
+    """The 7B-style Falcon block (one KV head, one LayerNorm) through the conversion functions."""
+    import weights2megatron as w2m
+    import megatron2hf as m2h
+    from transformers import FalconConfig, FalconForCausalLM
+    torch.manual_seed(4)
+    cfg = FalconConfig(vocab_size=128, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, multi_query=True,
+                       new_decoder_architecture=False, parallel_attn=True, bias=False, alibi=False)
+    hf = FalconForCausalLM(cfg).float().eval()
+    w2m.convert("falcon", 7, tmp_path / "mega", dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    lm, args = m2h.load_megatron(tmp_path / "mega")
+    assert args.parallel_attn and not args.parallel_layernorm and args.num_attention_heads_kv == 1
+    ref = hf.state_dict()
+    for k, v in m2h.falcon_state_dict(lm, args).items():
+        assert torch.equal(v, ref[k]), k
 
 
 def test_reshard_repads_the_vocabulary(tmp_path):

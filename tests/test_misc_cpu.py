@@ -116,3 +116,38 @@ def test_bench_argument_sets_of_all_baseline_configs_validate(monkeypatch):
         assert args.sequence_parallel and args.use_distributed_optimizer and args.bf16
         for k, v in expect.items():
             assert getattr(args, k) == v, (a.model, k, getattr(args, k))
+
+
+def test_example_scripts_only_use_flags_the_parsers_know():
+    """Every --flag in examples/**/*.sh is an option of the training parser, of one of the tool / task
+    command lines, of the launcher, or a short flag the wrapper script defines itself."""
+    import glob
+    import os
+    import re
+
+    import finetune
+    from epfl_megatron_b200.arguments import build_base_parser
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    parser = finetune.extra_args(build_base_parser())
+    known = {o for a in parser._actions for o in a.option_strings}
+    for f in ["tasks/main.py", "tasks/msdp/main.py", "tasks/msdp/preprocessing.py", "tools/run_text_generation_server.py",
+              "tools/checkpoint_util.py", "tools/checkpoint_loader_megatron.py", "tools/checkpoint_saver_megatron.py",
+              "tools/preprocess_data.py", "tools/merge_datasets.py", "tools/push_to_hub.py", "bench.py",
+              "weights2megatron/weights2megatron.py", "weights2megatron/megatron2hf.py", "verify_correctness.py",
+              "pretrain_ict.py", "pretrain_t5.py", "pretrain_bert.py"]:
+        src = open(os.path.join(root, f)).read()
+        for m in re.finditer(r'add_argument\(\s*"(--[A-Za-z0-9_-]+)"(?:,\s*"(--[A-Za-z0-9_-]+)")?', src):
+            known.update(x for x in m.groups() if x)
+    launcher = {"--nproc_per_node", "--nproc-per-node", "--nnodes", "--node_rank", "--node-rank", "--master_addr",
+                "--master_port", "--master-addr", "--master-port", "--nodes", "--ntasks-per-node", "--exclusive",
+                "--output", "--standalone", "--local-addr", "--help"}
+    scripts = sorted(glob.glob(os.path.join(root, "examples", "**", "*.sh"), recursive=True))
+    assert len(scripts) >= 35
+    unknown = {}
+    for f in scripts:
+        txt = open(f).read()
+        own = set(re.findall(r"(--[a-z-]+)\)", txt))          # case-statement flags of wrapper scripts
+        for tok in set(re.findall(r"(?<![\w-])(--[A-Za-z][A-Za-z0-9_-]*)", txt)):
+            if tok not in known and tok not in launcher and tok not in own:
+                unknown.setdefault(os.path.relpath(f, root), set()).add(tok)
+    assert not unknown, unknown

@@ -30,36 +30,33 @@ def build_pretraining_data_loader(dataset, consumed_samples, args=None):
 
 
 class MegatronPretrainingSampler:
+    """Sequential: sample ids consumed_samples, consumed_samples + 1, ... are cut into chunks of
+    micro_batch_size * dp; rank r yields rows [r * mbs, (r + 1) * mbs) of every chunk. An incomplete last
+    chunk is dropped unless ``drop_last`` is False (then every rank yields its, possibly short or empty, share)."""
+
     def __init__(self, total_samples, consumed_samples, micro_batch_size, data_parallel_rank,
                  data_parallel_size, drop_last=True):
+        if total_samples <= 0:
+            raise AssertionError(f"no sample to consume: {total_samples}")
+        if consumed_samples >= total_samples:
+            raise AssertionError(f"no samples left to consume: {consumed_samples}, {total_samples}")
+        if micro_batch_size <= 0 or not 0 <= data_parallel_rank < data_parallel_size:
+            raise AssertionError((micro_batch_size, data_parallel_rank, data_parallel_size))
         self.total_samples, self.consumed_samples = total_samples, consumed_samples
         self.micro_batch_size, self.data_parallel_rank = micro_batch_size, data_parallel_rank
-        self.micro_batch_times_data_parallel_size = micro_batch_size * data_parallel_size
+        self.chunk = micro_batch_size * data_parallel_size
         self.drop_last = drop_last
-        assert self.total_samples > 0, f"no sample to consume: {self.total_samples}"
-        assert self.consumed_samples < self.total_samples, \
-            f"no samples left to consume: {self.consumed_samples}, {self.total_samples}"
-        assert self.micro_batch_size > 0 and data_parallel_size > 0
-        assert self.data_parallel_rank < data_parallel_size
 
     def __len__(self):
         return self.total_samples
 
-    def get_start_end_idx(self):
-        lo = self.data_parallel_rank * self.micro_batch_size
-        return lo, lo + self.micro_batch_size
-
     def __iter__(self):
-        batch = []
-        for idx in range(self.consumed_samples, self.total_samples):
-            batch.append(idx)
-            if len(batch) == self.micro_batch_times_data_parallel_size:
-                lo, hi = self.get_start_end_idx()
-                yield batch[lo:hi]
-                batch = []
-        if batch and not self.drop_last:
-            lo, hi = self.get_start_end_idx()
-            yield batch[lo:hi]
+        mine = self.data_parallel_rank * self.micro_batch_size
+        for first in range(self.consumed_samples, self.total_samples, self.chunk):
+            last = min(first + self.chunk, self.total_samples)
+            if last - first < self.chunk and self.drop_last:
+                return
+            yield list(range(min(first + mine, last), min(first + mine + self.micro_batch_size, last)))
 
 
 class RandomSeedDataset(torch.utils.data.Dataset):
@@ -91,8 +88,8 @@ class MegatronPretrainingRandomSampler:
         self.micro_batch_size = micro_batch_size
         self.data_parallel_rank, self.data_parallel_size = data_parallel_rank, data_parallel_size
         self.data_sharding = data_sharding
-        self.micro_batch_times_data_parallel_size = micro_batch_size * data_parallel_size
-        self.last_batch_size = self.total_samples % self.micro_batch_times_data_parallel_size
+        self.chunk = micro_batch_size * data_parallel_size
+        self.last_batch_size = self.total_samples % self.chunk
         assert self.total_samples > 0 and self.micro_batch_size > 0 and data_parallel_size > 0
         assert self.data_parallel_rank < data_parallel_size
 
@@ -103,13 +100,13 @@ class MegatronPretrainingRandomSampler:
         active = self.total_samples - self.last_batch_size
         self.epoch = self.consumed_samples // active
         current = self.consumed_samples % active
-        assert current % self.micro_batch_times_data_parallel_size == 0
+        assert current % self.chunk == 0
         if isinstance(self.dataset, RandomSeedDataset):
             self.dataset.set_epoch(self.epoch)
         g = torch.Generator()
         g.manual_seed(self.epoch)
         if self.data_sharding:
-            bucket = (self.total_samples // self.micro_batch_times_data_parallel_size) * self.micro_batch_size
+            bucket = (self.total_samples // self.chunk) * self.micro_batch_size
             offset = current // self.data_parallel_size
             start = self.data_parallel_rank * bucket
             order = torch.randperm(bucket, generator=g).tolist()
@@ -122,6 +119,6 @@ class MegatronPretrainingRandomSampler:
         for idx in idx_range:
             batch.append(idx)
             if len(batch) == self.micro_batch_size:
-                self.consumed_samples += self.micro_batch_times_data_parallel_size
+                self.consumed_samples += self.chunk
                 yield batch
                 batch = []

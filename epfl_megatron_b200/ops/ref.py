@@ -12,16 +12,23 @@ import torch
 import torch.nn.functional as F
 
 
+def _norm_out_dtype(x, weight):
+    """An fp32 residual stream (--fp32_residual_connection) normalised with half-precision weights feeds
+    half-precision GEMMs: the output takes the weight's dtype, as the reference's mixed-dtype layer norm
+    does (model/fused_layer_norm.py:29-41, 106-122). Otherwise the input's dtype."""
+    return weight.dtype if x.dtype == torch.float32 and weight.dtype != torch.float32 else x.dtype
+
+
 def rmsnorm(x, weight, eps):
     """fp32 x*rsqrt(mean(x^2)+eps), cast back, THEN scale (model/fused_layer_norm.py:125-139)."""
     xf = x.float()
     y = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
-    return y.type_as(x) * weight
+    return (y.type_as(x) * weight).to(_norm_out_dtype(x, weight))
 
 
 def layernorm(x, weight, bias, eps):
     return F.layer_norm(x.float(), (x.shape[-1],), weight.float(),
-                        None if bias is None else bias.float(), eps).type_as(x)
+                        None if bias is None else bias.float(), eps).to(_norm_out_dtype(x, weight))
 
 
 def rope_table(head_dim: int, max_pos: int, theta: float = 10000.0, scaling_factor: float = 1.0,

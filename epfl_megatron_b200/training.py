@@ -169,8 +169,14 @@ def get_model(model_provider_func, model_type=ModelType.encoder_or_decoder, wrap
         model = [Float16Module(m, args) for m in model]
     if wrap_with_ddp:
         if args.DDP_impl == "torch":
-            model = [torchDDP(m, device_ids=[dev] if dev is not None else None, output_device=dev,
-                              process_group=mpu.get_data_parallel_group()) for m in model]
+            # torch-DDP semantics on the one gradient engine this framework has (the flat optimizers
+            # read the contiguous gradient buffers): gradients in the parameter dtype, averaged over
+            # the data-parallel group in 25 MiB buckets while the backward pass is still running
+            # (reference: training.py:284-288 wraps in torch.nn.parallel.DistributedDataParallel)
+            model = [LocalDDP(m, False, True, fuse_wgrad=False, overlap_grad_reduce=True, bucket_mb=25)
+                     for m in model]
+            for m in model:
+                m.fused_dp_required = False
         elif args.DDP_impl == "local":
             key_fn = make_group_key_fn(getattr(args, "_no_wd_cond", None), getattr(args, "_scale_lr_cond", None),
                                        getattr(args, "_lr_mult", 1.0))
@@ -269,7 +275,7 @@ def setup_model_and_optimizer(model_provider_func, model_type, no_wd_decay_cond=
 def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_scheduler, args=None):
     args = args or get_args()
     timers = get_timers()
-    if args.DDP_impl == "local" and args.use_contiguous_buffers_in_local_ddp:
+    if args.use_contiguous_buffers_in_local_ddp or args.DDP_impl == "torch":
         for part in model:
             part.zero_grad_buffer()
     optimizer.zero_grad()

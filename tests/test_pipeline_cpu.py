@@ -44,6 +44,15 @@ def test_dp2_overlapped_bucketed_grad_reduce_matches_single_reduce():
         _close(got, ref, 1e-5)
 
 
+def test_dp2_ddp_impl_torch_matches_local():
+    """--DDP_impl torch (parameter-dtype gradients averaged in 25 MiB buckets during backward) trains
+    like --DDP_impl local with one reduction after backward."""
+    kw = dict(KW, num_microbatches=2, layers=2)
+    ref = run_tiny(nproc=2, no_overlap=True, env_extra=ENV, **kw)["losses"]
+    got = run_tiny(nproc=2, extra="--DDP_impl=torch", env_extra=ENV, **kw)["losses"]
+    _close(got, ref, 1e-5)
+
+
 def test_dp_consistency_check_passes_and_catches_divergence():
     """--check_dp_consistency_interval: parameter checksums agree across replicas after every step;
     a replica whose weights were perturbed is reported."""

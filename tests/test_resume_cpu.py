@@ -35,3 +35,60 @@ def test_save_then_resume_matches_uninterrupted_run(tmp_path, nproc, dist_opt):
         assert "model_optim_rng.pt" in files, files
     second = run_tiny(steps=2, load=ckpt, **kw)["losses"]
     _close(second, full[2:])
+
+
+def _gpt_cli(tmp_path, nproc, extra, tp=1, pp=1):
+    """finetune.py on a tiny GPT (learned positions, biases, tied embeddings) -> stdout."""
+    import subprocess
+    import sys
+    from tests.helpers.launch import ROOT, free_port
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), **ENV)
+    argv = ["--model_name", "gpt", "--position_embedding_type", "absolute", "--num_layers", "4", "--hidden_size", "64",
+            "--num_attention_heads", "4", "--seq_length", "32", "--max_position_embeddings", "32",
+            "--micro_batch_size", "2", "--global_batch_size", "4", "--lr", "1e-3", "--min_lr", "1e-4",
+            "--lr_decay_style", "cosine", "--lr_decay_iters", "10", "--train_iters", "3",
+            "--tokenizer_type", "NullTokenizer", "--vocab_size", "1021", "--data_path", str(tmp_path / "corpus"),
+            "--split", "90,5,5", "--distributed_backend", "gloo", "--log_interval", "1", "--eval_interval", "100",
+            "--eval_iters", "2", "--num_workers", "0", "--use_cpu_initialization", "--no_bias_gelu_fusion",
+            "--no_masked_softmax_fusion", "--tensor_model_parallel_size", str(tp),
+            "--pipeline_model_parallel_size", str(pp)] + (["--sequence_parallel"] if tp > 1 else []) + extra
+    if nproc == 1:
+        env.update(RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+        cmd = [sys.executable, os.path.join(ROOT, "finetune.py")]
+    else:
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+               "--master-addr", "127.0.0.1", "--master-port", env["MASTER_PORT"], os.path.join(ROOT, "finetune.py")]
+    r = subprocess.run(cmd + argv, capture_output=True, text=True, env=env, cwd=ROOT, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    return r.stdout
+
+
+def _test_loss(out):
+    import re
+    m = re.search(r"end of training for test data \| lm loss value: ([0-9.E+-]+)", out)
+    assert m, out[-2000:]
+    return float(m.group(1))
+
+
+def test_trained_gpt_checkpoint_reshards_to_tp2_pp2_and_evaluates_the_same(tmp_path):
+    """The user workflow behind tools/checkpoint_util.py: train on one rank and save; reshard the
+    iteration checkpoint to tp 2 x pp 2; load it with the training entry point on four ranks. The
+    resharded checkpoint carries the integer iteration (nothing is re-trained) and the test-set loss
+    equals the one-rank loss of the same weights."""
+    import subprocess
+    import sys
+    from tests.helpers.launch import ROOT
+    from tests.test_cli_e2e_cpu import _corpus
+    _corpus(str(tmp_path / "corpus"))
+    trained = _gpt_cli(tmp_path, 1, ["--save", str(tmp_path / "ck"), "--save_interval", "3"])
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "checkpoint_util.py"), "--model_type", "GPT",
+                        "--load_dir", str(tmp_path / "ck"), "--save_dir", str(tmp_path / "ck22"),
+                        "--target_tensor_parallel_size", "2", "--target_pipeline_parallel_size", "2"],
+                       capture_output=True, text=True, cwd=ROOT, env=dict(os.environ, **ENV))
+    assert r.returncode == 0, r.stderr[-3000:]
+    assert open(tmp_path / "ck22" / "latest_checkpointed_iteration.txt").read().strip() == "3"
+    assert sorted(os.listdir(tmp_path / "ck22" / "iter_0000003")) == [
+        "mp_rank_00_000", "mp_rank_00_001", "mp_rank_01_000", "mp_rank_01_001"]
+    sharded = _gpt_cli(tmp_path, 4, ["--load", str(tmp_path / "ck22"), "--no_load_optim", "--no_load_rng"], tp=2, pp=2)
+    assert "at iteration 3" in sharded and not [l for l in sharded.splitlines() if l.startswith(" iteration ")]
+    assert abs(_test_loss(sharded) - _test_loss(trained)) <= 2e-5 * _test_loss(trained)

@@ -29,7 +29,9 @@ from epfl_megatron_b200.utils.ckpt_convert import (layer_index, merge_tp, normal
 def _tracker(load_dir):
     with open(os.path.join(load_dir, "latest_checkpointed_iteration.txt")) as f:
         it = f.read().strip()
-    return it, ("release" if it == "release" else f"iter_{int(it):07d}")
+    if it != "release":
+        it = int(it)            # the training loop compares the stored iteration with integers
+    return it, ("release" if it == "release" else f"iter_{it:07d}")
 
 
 def _rank_dir(tp_rank, pp_rank, pp):

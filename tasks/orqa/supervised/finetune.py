@@ -18,8 +18,9 @@ from orqa.supervised.eval_utils import accuracy_func_provider, process_batch, ta
 
 
 def get_group_world_size_rank():
+    """-> (data-parallel group, this rank's index in it, its size)."""
     group = mpu.get_data_parallel_group()
-    return group, dist.get_world_size(group=group), dist.get_rank(group=group)
+    return group, dist.get_rank(group=group), dist.get_world_size(group=group)
 
 
 def check_and_append_tensor_for_gather(group, rank, world_size, input_):

@@ -7,6 +7,7 @@ import subprocess
 import sys
 
 import numpy as np
+import pytest
 
 from tests.helpers.launch import free_port
 
@@ -209,3 +210,54 @@ def test_msdp_preprocessing_and_f1(tmp_path):
     # first pair: articles / punctuation dropped -> guess {kernel,is,gpu,function}, 4 of 4 in the answer
     assert 0.4 < p < 0.6 and 0.25 < r < 0.45 and 0.3 < f1 < 0.5
     assert F1Metric.compute_each_pair("same words here", "same words here")[2] == 1.0
+
+
+@pytest.mark.parametrize("nproc", [1, 2])
+def test_orqa_supervised_retriever_finetune_cli(tmp_path, nproc):
+    """tasks/main.py --task RET-FINETUNE-NQ on DPR-format json: biencoder with in-batch negatives gathered
+    over the data-parallel group plus one hard negative per query. With near-identical random embeddings
+    the loss starts at log(#contexts scored per query) = log(nproc * (4 positives + 4 negatives)); the
+    end-of-epoch callback reports the average rank and top-k accuracy on the validation file."""
+    import math
+    import re
+    words = "the of and to in a is that for it as was with be by on not he this are".split()
+    (tmp_path / "vocab.txt").write_text("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words) + "\n")
+    rng = np.random.RandomState(0)
+
+    def ctx():
+        return {"title": " ".join(rng.choice(words, 2)), "text": " ".join(rng.choice(words, 8))}
+
+    def rows(n):
+        return [{"question": " ".join(rng.choice(words, 5)) + "?", "answers": [str(rng.choice(words))],
+                 "positive_ctxs": [ctx()], "hard_negative_ctxs": [ctx(), ctx()], "negative_ctxs": [ctx(), ctx()]}
+                for _ in range(n)]
+    (tmp_path / "train.json").write_text(json.dumps(rows(16)))
+    (tmp_path / "dev.json").write_text(json.dumps(rows(8)))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), B200_DISABLE_KERNELS="1",
+               CUDA_VISIBLE_DEVICES="")
+    if nproc == 1:
+        env.update(RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+        launcher = [sys.executable]
+    else:
+        launcher = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+                    "--master-addr", "127.0.0.1", "--master-port", env["MASTER_PORT"]]
+    cmd = launcher + [
+        os.path.join(ROOT, "tasks", "main.py"), "--task", "RET-FINETUNE-NQ", "--epochs", "1",
+        "--train_data", str(tmp_path / "train.json"), "--valid_data", str(tmp_path / "dev.json"),
+        "--tokenizer_type", "BertWordPieceLowerCase", "--vocab_file", str(tmp_path / "vocab.txt"),
+        "--num_layers", "2", "--hidden_size", "32", "--num_attention_heads", "2", "--seq_length", "32",
+        "--retriever_seq_length", "32", "--max_position_embeddings", "32", "--micro_batch_size", "4",
+        "--global_batch_size", str(4 * nproc), "--lr", "1e-3", "--lr_decay_style", "linear",
+        "--lr_warmup_fraction", "0.1", "--distributed_backend", "gloo", "--use_cpu_initialization",
+        "--no_bias_gelu_fusion", "--no_masked_softmax_fusion", "--num_workers", "0", "--log_interval", "1",
+        "--eval_interval", "100", "--eval_iters", "1", "--make_vocab_size_divisible_by", "8",
+        "--hidden_dropout", "0.0", "--attention_dropout", "0.0", "--retriever_report_topk_accuracies", "1", "2",
+        "--retriever_score_scaling", "--train_with_neg", "--train_hard_neg", "1", "--val_av_rank_hard_neg", "2",
+        "--val_av_rank_other_neg", "2", "--eval_micro_batch_size", "4", "--biencoder_projection_dim", "16"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    losses = [float(x) for x in re.findall(r"\| loss: ([0-9.E+-]+)", r.stdout)]
+    assert len(losses) == 16 // (4 * nproc)
+    assert abs(losses[0] - math.log(8 * nproc)) < 5e-3, losses
+    assert re.search(r"epoch:0 name:dev rank: [0-9.]+ top1_acc: [0-9.]+ top2_acc: [0-9.]+", r.stdout), r.stdout[-800:]
+    assert "done :-)" in r.stdout

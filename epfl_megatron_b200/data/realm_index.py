@@ -60,11 +60,15 @@ class OpenRetreivalDataStore:
             pickle.dump(self.state(), f)
 
     def merge_shards_and_save(self):
-        """Rank 0 only: fold every shard into one pickle and remove the temp dir."""
+        """Rank 0 only: fold every shard into one pickle and remove the temp dir. The merging rank's
+        own shard is already in memory when it embedded blocks itself (megatron/data/realm_index.py:86-115)."""
         seen = set()
+        own_in_memory = bool(self.embed_data)
         for fname in os.listdir(self.temp_dir_name):
             rank = int(os.path.splitext(fname)[0])
             seen.add(rank)
+            if own_in_memory and rank == self.rank:
+                continue
             with open(f"{self.temp_dir_name}/{fname}", "rb") as f:
                 data = pickle.load(f)
                 before, n = len(self.embed_data), len(data["embed_data"])

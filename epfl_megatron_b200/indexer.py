@@ -14,7 +14,7 @@ from .data.realm_index import OpenRetreivalDataStore, detach
 from .models.biencoder_model import get_model_provider
 from .parallel import state as mpu
 from .training import get_model
-from .utils import print_rank_0, unwrap_model
+from .utils import print_rank_0, unwrap_to
 
 
 class IndexBuilder:
@@ -51,7 +51,7 @@ class IndexBuilder:
             print(f"Batch {self.iteration:10d} | Total {self.total_processed:10d}", flush=True)
 
     def build_and_save_index(self):
-        model = unwrap_model(self.model[0])
+        model = unwrap_to(self.model[0], "embed_text")
         model.eval()
         while True:
             try:

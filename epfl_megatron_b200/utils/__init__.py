@@ -18,6 +18,13 @@ def unwrap_model(model, module_instances=(torchDDP,)):
     return _u(model, module_instances)
 
 
+def unwrap_to(model, attribute):
+    """Peel wrappers (DDP, Float16Module, ...) until the module that has ``attribute``."""
+    while not hasattr(model, attribute):
+        model = model.module
+    return model
+
+
 def calc_params_l2_norm(model):
     """L2 norm of all (non-duplicated) parameters across the model-parallel group."""
     from ..models.module import param_is_not_shared

@@ -11,7 +11,7 @@ from epfl_megatron_b200.data.realm_index import FaissMIPSIndex, OpenRetreivalDat
 from epfl_megatron_b200.models.biencoder_model import get_model_provider
 from epfl_megatron_b200.parallel import state as mpu
 from epfl_megatron_b200.training import get_model
-from epfl_megatron_b200.utils import unwrap_model
+from epfl_megatron_b200.utils import unwrap_to
 from orqa.unsupervised.nq import get_nq_dataset, get_one_epoch_nq_dataloader, process_nq_batch
 from orqa.unsupervised.qa_utils import calculate_matches
 
@@ -63,7 +63,7 @@ class ORQAEvaluator:
         for batch in loader:
             tokens, mask, types, _, refs = process_nq_batch(batch)
             assert len(self.model) == 1
-            um = unwrap_model(self.model[0])
+            um = unwrap_to(self.model[0], "embed_text")
             with torch.no_grad():
                 q = um.embed_text(um.query_model, tokens.to(_dev()), mask.to(_dev()), types.to(_dev()))
             reference.extend(refs)

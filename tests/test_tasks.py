@@ -261,3 +261,74 @@ def test_orqa_supervised_retriever_finetune_cli(tmp_path, nproc):
     assert abs(losses[0] - math.log(8 * nproc)) < 5e-3, losses
     assert re.search(r"epoch:0 name:dev rank: [0-9.]+ top1_acc: [0-9.]+ top2_acc: [0-9.]+", r.stdout), r.stdout[-800:]
     assert "done :-)" in r.stdout
+
+
+def test_open_retrieval_pipeline_ict_pretrain_index_evaluate(tmp_path):
+    """The open-retrieval workflow end to end: pretrain_ict.py saves a biencoder; IndexBuilder embeds an
+    evidence TSV with the context tower on TWO data-parallel ranks (each dumps a shard, rank 0 folds
+    the other's into its own and writes --embedding_path); tasks/main.py --task RETRIEVER-EVAL embeds
+    the questions with the query tower, searches the index and reports top-k answer hits."""
+    import pickle
+    import re
+    sys.path.insert(0, os.path.join(ROOT, "tests", "helpers"))
+    try:
+        import legacy_worker
+    finally:
+        sys.path.pop(0)
+    vf, prefix, titles = legacy_worker.make_corpus(str(tmp_path))
+    words = [w for w in open(vf).read().split() if not w.startswith("[")][:30]
+    rng = np.random.RandomState(0)
+    model = (f"--num_layers 2 --hidden_size 64 --num_attention_heads 4 --seq_length 48 --max_position_embeddings 64 "
+             f"--micro_batch_size 4 --tokenizer_type BertWordPieceLowerCase --vocab_file {vf} "
+             f"--distributed_backend gloo --use_cpu_initialization --hidden_dropout 0.0 --attention_dropout 0.0 "
+             f"--no_bias_gelu_fusion --no_masked_softmax_fusion --num_workers 0 --make_vocab_size_divisible_by 8 "
+             f"--biencoder_projection_dim 32 --retriever_score_scaling --retriever_report_topk_accuracies 1 2 5 "
+             f"--retriever_seq_length 48").split()
+
+    def run(script, extra, nproc=1):
+        env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), B200_DISABLE_KERNELS="1",
+                   CUDA_VISIBLE_DEVICES="")
+        if nproc == 1:
+            env.update(RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+            launcher = [sys.executable]
+        else:
+            launcher = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+                        "--master-addr", "127.0.0.1", "--master-port", env["MASTER_PORT"]]
+        r = subprocess.run(launcher + [script] + model + extra.split(), capture_output=True, text=True,
+                           timeout=900, env=env, cwd=ROOT)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3500:]
+        return r.stdout
+
+    ckpt = tmp_path / "ckpt"
+    run(os.path.join(ROOT, "pretrain_ict.py"),
+        f"--global_batch_size 4 --train_iters 4 --lr 2e-3 --min_lr 1e-4 --lr_decay_style constant --data_path {prefix} "
+        f"--titles_data_path {titles} --split 90,5,5 --eval_iters 1 --eval_interval 2 --log_interval 2 "
+        f"--data_impl mmap --seed 7 --save {ckpt} --save_interval 4 --query_in_block_prob 0.2 --ict_head_size 32")
+    with open(tmp_path / "evidence.tsv", "w") as f:
+        f.write("id\ttext\ttitle\n")
+        for i in range(1, 21):
+            f.write(f"{i}\t{' '.join(rng.choice(words, 12))}\t{' '.join(rng.choice(words, 2))}\n")
+    with open(tmp_path / "qa.csv", "w") as f:
+        for _ in range(6):
+            f.write(f"{' '.join(rng.choice(words, 5))}?\t{json.dumps([str(rng.choice(words))])}\n")
+    (tmp_path / "build_index.py").write_text(
+        f"import sys\nsys.path.insert(0, {ROOT!r})\n"
+        "from epfl_megatron_b200.initialize import initialize_megatron\n"
+        "from epfl_megatron_b200.indexer import IndexBuilder\n"
+        "initialize_megatron()\nIndexBuilder().build_and_save_index()\n")
+    shared = (f"--load {ckpt} --ict_load {ckpt} --evidence_data_path {tmp_path / 'evidence.tsv'} "
+              f"--embedding_path {tmp_path / 'emb.pkl'}")
+    out = run(str(tmp_path / "build_index.py"), shared + " --indexer_batch_size 4 --indexer_log_interval 1", nproc=2)
+    assert "Finished merging 2 shards for a total of 20 embeds" in out, out[-1500:]
+    with open(tmp_path / "emb.pkl", "rb") as f:
+        embeds = pickle.load(f)["embed_data"]
+    assert sorted(embeds) == list(range(1, 21)) and all(v.shape == (32,) for v in embeds.values())
+    assert not os.path.exists(tmp_path / "emb_tmp")
+    out = run(os.path.join(ROOT, "tasks", "main.py"),
+              "--task RETRIEVER-EVAL " + shared + f" --qa_data_dev {tmp_path / 'qa.csv'} --faiss_topk_retrievals 5 "
+              "--faiss_match string")
+    hits = re.search(r"topk-5 documents hits \[([0-9, ]+)\]", out)
+    assert hits, out[-1500:]
+    hits = [int(x) for x in hits.group(1).split(",")]
+    assert len(hits) == 5 and hits == sorted(hits) and hits[-1] <= 6
+    assert re.search(r"top-5: [0-9.]+", out) and "done :-)" in out

@@ -332,3 +332,42 @@ def test_open_retrieval_pipeline_ict_pretrain_index_evaluate(tmp_path):
     hits = [int(x) for x in hits.group(1).split(",")]
     assert len(hits) == 5 and hits == sorted(hits) and hits[-1] <= 6
     assert re.search(r"top-5: [0-9.]+", out) and "done :-)" in out
+
+
+@pytest.mark.parametrize("prompt_type", ["knowledge", "response"])
+def test_msdp_prompt_cli_generates_one_line_per_sample(tmp_path, prompt_type):
+    """tasks/msdp/main.py --task MSDP-PROMPT with a locally built (random, tiny) GPT: the few-shot prompt
+    is assembled per test sample, greedy generation runs through the public generation API and the
+    first generated line of every sample lands in --sample_output_file."""
+    words = ["alpha", "beta", "gamma", "delta", "kernel", "tensor", "memory", "stream", "token", "layer"]
+    text = "".join(words) + " .=()>:Topic: . User says: We know that: System replies:"
+    toks = list(dict.fromkeys([c if c != " " else "Ġ" for c in sorted(set(text))] + ["Ċ", "<|endoftext|>"]))
+    (tmp_path / "vocab.json").write_text(json.dumps({t: i for i, t in enumerate(toks)}))
+    (tmp_path / "merges.txt").write_text("#version: 0.2\n")
+    samples = [("alpha", "beta gamma", "delta kernel"), ("tensor", "memory stream", "token layer"),
+               ("layer", "token alpha", "beta")]
+    with open(tmp_path / "test.txt", "w") as f:
+        for topic, last, know in samples:
+            f.write(f"{topic}\talpha [SEP] {last}\t{know}\tgamma\n")
+    if prompt_type == "knowledge":
+        with open(tmp_path / "prompts", "w") as f:
+            for topic, last, know in samples:
+                f.write(json.dumps({f"{topic} {last}": [f"( {last} ) {topic} => {know}"] * 2}) + "\n")
+    else:
+        (tmp_path / "prompts").write_text(
+            "Topic: alpha. User says: beta We know that: gamma System replies: delta\n" * 2)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    cmd = [sys.executable, os.path.join(ROOT, "tasks", "msdp", "main.py"), "--task", "MSDP-PROMPT",
+           "--prompt_type", prompt_type, "--prompt_file", str(tmp_path / "prompts"),
+           "--sample_input_file", str(tmp_path / "test.txt"), "--sample_output_file", str(tmp_path / "out.txt"),
+           "--num_prompt_examples", "2", "--out_seq_length", "8", "--tokenizer_type", "GPT2BPETokenizer",
+           "--vocab_file", str(tmp_path / "vocab.json"), "--merge_file", str(tmp_path / "merges.txt"),
+           "--num_layers", "2", "--hidden_size", "64", "--num_attention_heads", "4", "--seq_length", "256",
+           "--max_position_embeddings", "256", "--micro_batch_size", "1", "--distributed_backend", "gloo",
+           "--use_cpu_initialization", "--no_load_optim", "--no_load_rng", "--num_workers", "0"]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, cwd=ROOT, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    lines = open(tmp_path / "out.txt").read().split("\n")
+    assert len(lines) == len(samples) + 1 and lines[-1] == ""
+    assert all(len(ln) <= 8 for ln in lines)        # at most --out_seq_length single-character tokens

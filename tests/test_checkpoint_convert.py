@@ -499,3 +499,40 @@ def test_reshard_repads_the_vocabulary(tmp_path):
     s0 = torch.load(out4 / "release" / "mp_rank_00" / "model_optim_rng.pt", weights_only=False)
     assert s0["args"].padded_vocab_size == 256
     assert s0["model"]["language_model"]["embedding"]["word_embeddings"]["weight"].shape == (64, 64)
+
+
+@pytest.mark.parametrize("new_arch,kv_heads", [(True, 2), (False, 1)])
+def test_verify_correctness_cli_falcon(tmp_path, new_arch, kv_heads):
+    """verify_correctness.py --model_name falcon for both Falcon layouts (40B-style grouped KV with two
+    layer norms, 7B-style multi-query with one): converted weights reproduce the HF logits."""
+    import re
+    import numpy as np
+    import weights2megatron as w2m
+    from transformers import FalconConfig, FalconForCausalLM
+    from epfl_megatron_b200.data import indexed_dataset as ids
+    from tests.helpers.launch import free_port
+    torch.manual_seed(0)
+    cfg = FalconConfig(vocab_size=256, hidden_size=64, num_hidden_layers=2, num_attention_heads=4,
+                       num_kv_heads=kv_heads, new_decoder_architecture=new_arch, multi_query=not new_arch,
+                       parallel_attn=True, bias=False, alibi=False)
+    hf = FalconForCausalLM(cfg).float().eval()
+    hf.save_pretrained(tmp_path / "hf")
+    w2m.convert("falcon", 7, tmp_path / "mega", dtype=torch.float32, state_dict=hf.state_dict(), config=cfg)
+    rng = np.random.default_rng(0)
+    b = ids.MMapIndexedDatasetBuilder(ids.data_file_path(str(tmp_path / "corpus")), dtype=np.uint16)
+    for _ in range(100):
+        b.add_item(torch.tensor(rng.integers(1, 250, size=int(rng.integers(30, 120)))))
+        b.end_document()
+    b.finalize(ids.index_file_path(str(tmp_path / "corpus")))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    cmd = [sys.executable, os.path.join(ROOT, "verify_correctness.py"), "--model_name", "falcon",
+           "--load", str(tmp_path / "mega"), "--data_path", str(tmp_path / "corpus"), "--split", "100,0,0",
+           "--tokenizer_type", "NullTokenizer", "--vocab_size", "256", "--make_vocab_size_divisible_by", "1",
+           "--huggingface_cache", str(tmp_path / "hf"), "--verify_batches", "2", "--distributed_backend", "gloo",
+           "--use_cpu_initialization", "--no_load_optim", "--no_load_rng", "--num_workers", "0", "--eval_iters", "0",
+           "--seq_length", "64", "--max_position_embeddings", "64"]
+    r = subprocess.run(cmd, capture_output=True, text=True, env=env, cwd=ROOT, timeout=600)
+    assert r.returncode == 0, r.stdout[-2500:] + r.stderr[-2500:]
+    maxima = [float(x) for x in re.findall(r"Max absoulute error in the logits: max=([0-9.]+)", r.stdout)]
+    assert len(maxima) == 2 and max(maxima) <= 1e-3, r.stdout[-1500:]

@@ -60,7 +60,8 @@ class MegatronModule(torch.nn.Module):
             torch.distributed.all_reduce(self.word_embeddings_weight().data, group=mpu.get_embedding_group())
         if mpu.is_rank_in_position_embedding_group() and \
                 args.pipeline_model_parallel_split_rank is not None:
-            self.language_model.embedding.cuda()
+            if torch.cuda.is_available() and args.distributed_backend != "gloo":
+                self.language_model.embedding.cuda()
             pos = self.language_model.embedding.position_embeddings
             torch.distributed.all_reduce(pos.weight.data, group=mpu.get_position_embedding_group())
 

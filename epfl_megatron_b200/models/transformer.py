@@ -401,6 +401,9 @@ class NoopTransformerLayer(MegatronModule):
 def _get_num_layers(args, is_encoder_and_decoder_model, is_decoder=False):
     """Transformer layers owned by this pipeline rank (transformer.py:844-893 behaviour)."""
     pp = mpu.get_pipeline_model_parallel_world_size()
+    # the reference leaves decoder_num_layers unset unless the flag is given (its T5 recipes
+    # only pass --num_layers); an unset value means "as deep as the encoder"
+    dec = args.decoder_num_layers if args.decoder_num_layers is not None else args.encoder_num_layers
     if pp > 1:
         if is_encoder_and_decoder_model:
             assert args.pipeline_model_parallel_split_rank is not None
@@ -408,12 +411,12 @@ def _get_num_layers(args, is_encoder_and_decoder_model, is_decoder=False):
                            else args.pipeline_model_parallel_split_rank)
             n_dec_ranks = args.transformer_pipeline_model_parallel_size - n_enc_ranks
             assert args.encoder_num_layers % n_enc_ranks == 0
-            assert args.decoder_num_layers % n_dec_ranks == 0
+            assert dec % n_dec_ranks == 0
             if mpu.is_pipeline_stage_before_split():
                 n = 0 if args.standalone_embedding_stage and mpu.get_pipeline_model_parallel_rank() == 0 \
                     else args.encoder_num_layers // n_enc_ranks
             else:
-                n = args.decoder_num_layers // n_dec_ranks
+                n = dec // n_dec_ranks
         else:
             assert args.num_layers == args.encoder_num_layers
             assert args.num_layers % args.transformer_pipeline_model_parallel_size == 0, \
@@ -421,9 +424,6 @@ def _get_num_layers(args, is_encoder_and_decoder_model, is_decoder=False):
             n = 0 if args.standalone_embedding_stage and mpu.get_pipeline_model_parallel_rank() == 0 \
                 else args.num_layers // args.transformer_pipeline_model_parallel_size
     else:
-        # the reference leaves decoder_num_layers unset unless the flag is given (its T5 recipes
-        # only pass --num_layers); an unset value means "as deep as the encoder"
-        dec = args.decoder_num_layers if args.decoder_num_layers is not None else args.encoder_num_layers
         n = dec if is_decoder else args.encoder_num_layers
     return n
 

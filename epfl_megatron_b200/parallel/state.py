@@ -93,6 +93,9 @@ def initialize_model_parallel(tensor_model_parallel_size: int = 1,
         pos_groups.append(p)
     _EMB, _EMB_RANKS = make(emb_groups)
     _POS_EMB, _POS_EMB_RANKS = make(pos_groups)
+    # a middle pipeline stage belongs to neither group: an empty list, not the "uninitialised" None
+    _EMB_RANKS = _EMB_RANKS or []
+    _POS_EMB_RANKS = _POS_EMB_RANKS or []
     _set_global_memory_buffer()
 
 

@@ -63,3 +63,35 @@ def test_legacy_entry_points_from_the_command_line(script, extra, tmp_path):
     assert r.returncode == 0, r.stdout[-2500:] + r.stderr[-3500:]
     assert "iteration        4/       4" in r.stdout and "validation loss at iteration 2" in r.stdout, r.stdout[-2000:]
     assert open(tmp_path / "ckpt" / "latest_checkpointed_iteration.txt").read().strip() == "4"
+
+
+@pytest.mark.parametrize("stages,split,layers", [(2, 1, 2), (4, 2, 4)])
+def test_t5_encoder_decoder_pipeline_split(tmp_path, stages, split, layers):
+    """pretrain_t5.py with the encoder on the pipeline ranks before --pipeline_model_parallel_split_rank
+    and the decoder after it. --decoder_num_layers is not given (the reference's T5 recipes pass only
+    --num_layers): the decoder is as deep as the encoder. With four stages the middle ranks hold
+    neither embedding copy and stay out of the embedding-group all-reduces."""
+    import re
+    sys.path.insert(0, os.path.join(ROOT, "tests", "helpers"))
+    try:
+        import legacy_worker
+    finally:
+        sys.path.pop(0)
+    vf, prefix, _ = legacy_worker.make_corpus(str(tmp_path))
+    argv = (f"--num_layers {layers} --hidden_size 64 --num_attention_heads 4 --seq_length 48 --max_position_embeddings 64 "
+            f"--micro_batch_size 2 --global_batch_size 4 --train_iters 3 --lr 2e-3 --min_lr 1e-4 "
+            f"--lr_decay_style constant --tokenizer_type BertWordPieceLowerCase --vocab_file {vf} --data_path {prefix} "
+            f"--split 90,5,5 --distributed_backend gloo --use_cpu_initialization --hidden_dropout 0.0 "
+            f"--attention_dropout 0.0 --no_bias_gelu_fusion --no_masked_softmax_fusion --num_workers 0 "
+            f"--eval_iters 1 --eval_interval 2 --log_interval 1 --make_vocab_size_divisible_by 8 --data_impl mmap "
+            f"--seed 7 --decoder_seq_length 32 --vocab_extra_ids 100 --kv_channels 16 --ffn_hidden_size 128 "
+            f"--pipeline_model_parallel_size {stages} --pipeline_model_parallel_split_rank {split}").split()
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), B200_DISABLE_KERNELS="1",
+               CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={stages}",
+           "--master-addr", "127.0.0.1", "--master-port", env["MASTER_PORT"], os.path.join(ROOT, "pretrain_t5.py")]
+    r = subprocess.run(cmd + argv, capture_output=True, text=True, timeout=900, env=env, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3500:]
+    losses = [float(x) for x in re.findall(r"\| lm loss: ([0-9.E+-]+)", r.stdout)]
+    assert len(losses) >= 3 and losses[-1] < losses[0], r.stdout[-1500:]
+    assert "validation loss at iteration 2" in r.stdout

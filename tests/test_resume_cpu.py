@@ -92,3 +92,28 @@ def test_trained_gpt_checkpoint_reshards_to_tp2_pp2_and_evaluates_the_same(tmp_p
     sharded = _gpt_cli(tmp_path, 4, ["--load", str(tmp_path / "ck22"), "--no_load_optim", "--no_load_rng"], tp=2, pp=2)
     assert "at iteration 3" in sharded and not [l for l in sharded.splitlines() if l.startswith(" iteration ")]
     assert abs(_test_loss(sharded) - _test_loss(trained)) <= 2e-5 * _test_loss(trained)
+
+
+def test_gpt_tied_embeddings_on_four_pipeline_stages(tmp_path):
+    """Tied input/output embeddings with MIDDLE pipeline stages present: only the first and last stage
+    are in the embedding group (the middle ones must stay out of its all-reduces), and after training
+    the last stage's head copy still equals the first stage's embedding table."""
+    import torch
+    from tests.test_cli_e2e_cpu import _corpus
+    _corpus(str(tmp_path / "corpus"))
+    out = _gpt_cli(tmp_path, 4, ["--save", str(tmp_path / "ck"), "--save_interval", "3", "--hidden_dropout", "0",
+                                 "--attention_dropout", "0"], pp=4)
+    import re
+    losses = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
+    assert len(losses) >= 3 and losses[2] < losses[0], losses
+    import megatron  # noqa: F401  (lets torch.load resolve the pickled argument classes)
+    first = torch.load(tmp_path / "ck" / "iter_0000003" / "mp_rank_00_000" / "model_optim_rng.pt",
+                       map_location="cpu", weights_only=False)["model"]
+    last = torch.load(tmp_path / "ck" / "iter_0000003" / "mp_rank_00_003" / "model_optim_rng.pt",
+                      map_location="cpu", weights_only=False)["model"]
+    table = first["language_model"]["embedding"]["word_embeddings"]["weight"]
+    head = last["word_embeddings_for_head"]["weight"]
+    assert torch.equal(table, head)
+    middle = torch.load(tmp_path / "ck" / "iter_0000003" / "mp_rank_00_001" / "model_optim_rng.pt",
+                        map_location="cpu", weights_only=False)["model"]
+    assert "word_embeddings_for_head" not in middle and "embedding" not in middle["language_model"]

@@ -110,3 +110,82 @@ def test_server_cli_tensor_parallel_and_client(tmp_path):
         except subprocess.TimeoutExpired:
             server.kill()
         log.close()
+
+
+def _serve_and_query(tmp_path, tag, nproc, model_args, extra, bodies):
+    """Start tools/run_text_generation_server.py on ``nproc`` ranks, PUT every body to /api, stop it."""
+    import socket
+    import time
+    import urllib.request
+    port = free_port()
+    env = dict(os.environ, B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr",
+           "127.0.0.1", "--master-port", str(free_port()),
+           os.path.join(ROOT, "tools", "run_text_generation_server.py")] + model_args + extra + [
+        "--host", "127.0.0.1", "--port", str(port)]
+    log_path = tmp_path / f"server_{tag}.log"
+    log = open(log_path, "w")
+    server = subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT, env=env, cwd=ROOT)
+    try:
+        deadline = time.time() + 180
+        while True:
+            assert server.poll() is None and time.time() < deadline, open(log_path).read()[-3000:]
+            try:
+                socket.create_connection(("127.0.0.1", port), timeout=1).close()
+                break
+            except OSError:
+                time.sleep(1)
+        answers = []
+        for body in bodies:
+            req = urllib.request.Request(f"http://127.0.0.1:{port}/api", method="PUT", data=json.dumps(body).encode(),
+                                         headers={"Content-Type": "application/json"})
+            with urllib.request.urlopen(req, timeout=180) as resp:
+                answers.append(json.loads(resp.read().decode()))
+        return answers
+    finally:
+        server.terminate()
+        try:
+            server.wait(timeout=30)
+        except subprocess.TimeoutExpired:
+            server.kill()
+        log.close()
+
+
+def test_pipeline_parallel_server_matches_single_rank(tmp_path):
+    """The same trained weights served from one rank and, resharded by tools/checkpoint_util.py, from two
+    pipeline stages: greedy sampling with log-probabilities, beam search and prompt scoring return
+    identical text and log-probabilities (megatron/text_generation/forward_step.py pipelined path)."""
+    from tests.test_cli_e2e_cpu import _corpus
+    _corpus(str(tmp_path / "corpus"))
+    model = ["--model_name", "llama2", "--num_layers", "4", "--hidden_size", "64", "--num_attention_heads", "4",
+             "--num_attention_heads_kv", "2", "--ffn_hidden_size", "128", "--seq_length", "32",
+             "--max_position_embeddings", "32", "--micro_batch_size", "2", "--use_rms_norm", "--glu_activation", "swiglu",
+             "--no_tie_embed_logits", "--position_embedding_type", "rotary", "--no_bias_gelu_fusion",
+             "--hidden_dropout", "0", "--attention_dropout", "0", "--tokenizer_type", "NullTokenizer",
+             "--vocab_size", "1021", "--distributed_backend", "gloo", "--use_cpu_initialization"]
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1", MASTER_ADDR="127.0.0.1",
+               MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "finetune.py")] + model + [
+        "--global_batch_size", "4", "--lr", "1e-3", "--train_iters", "2", "--data_path", str(tmp_path / "corpus"),
+        "--split", "90,5,5", "--log_interval", "1", "--eval_iters", "0", "--num_workers", "0",
+        "--save", str(tmp_path / "ck"), "--save_interval", "2"], capture_output=True, text=True, env=env, cwd=ROOT,
+        timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "checkpoint_util.py"), "--model_type", "llama2",
+                        "--load_dir", str(tmp_path / "ck"), "--save_dir", str(tmp_path / "ck_pp2"),
+                        "--target_tensor_parallel_size", "1", "--target_pipeline_parallel_size", "2"],
+                       capture_output=True, text=True, cwd=ROOT, env=env)
+    assert r.returncode == 0, r.stderr[-3000:]
+    bodies = [{"prompts": ["5 6 7 8", "9 10"], "tokens_to_generate": 6, "top_k": 1, "logprobs": True},
+              {"prompts": ["5 6 7 8"], "tokens_to_generate": 4, "beam_width": 2},
+              {"prompts": ["5 6 7 8 9 10 11"], "tokens_to_generate": 0, "logprobs": True}]
+    load = ["--no_load_optim", "--no_load_rng", "--load"]
+    one = _serve_and_query(tmp_path, "pp1", 1, model, load + [str(tmp_path / "ck")], bodies)
+    two = _serve_and_query(tmp_path, "pp2", 2, model,
+                           ["--pipeline_model_parallel_size", "2"] + load + [str(tmp_path / "ck_pp2")], bodies)
+    assert len(one[0]["text"][0].split()) == 10 and len(one[1]["text"]) == 2
+    for a, b in zip(one, two):
+        assert a["text"] == b["text"]
+        if a.get("logprobs"):
+            flat_a, flat_b = torch.tensor(a["logprobs"][0]), torch.tensor(b["logprobs"][0])
+            assert torch.allclose(flat_a, flat_b, atol=1e-5)

@@ -217,9 +217,11 @@ def _fused_dp_enabled(args, dev) -> bool:
 
 
 def _get_optimizer_param_scheduler(optimizer, args):
-    if args.train_iters:
+    if args.train_iters or (args.train_iters == 0 and not args.train_samples):
+        # train_iters == 0: evaluation-only runs of the task harness (--epochs 0) still build an
+        # optimizer and a schedule; give the schedule a nominal length of one step
         if args.lr_decay_iters is None:
-            args.lr_decay_iters = args.train_iters
+            args.lr_decay_iters = max(args.train_iters, 1)
         lr_decay_steps = args.lr_decay_iters * args.global_batch_size
         wd_incr_steps = args.train_iters * args.global_batch_size
         warm = (args.lr_warmup_fraction * lr_decay_steps if args.lr_warmup_fraction is not None

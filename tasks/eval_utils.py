@@ -41,8 +41,11 @@ def accuracy_func_provider(single_dataset_provider):
             print(" >> |epoch: {}| overall: correct / total = {} / {} = {:.4f} %".format(
                 epoch, correct, total, 100.0 * correct / max(total, 1)))
         if output_predictions and is_last_rank():
-            assert args.load is not None
-            torch.save(named, os.path.join(args.load, "predictions.pt"))
+            # next to the evaluated checkpoint (the reference insists on --load; an evaluation-only run
+            # usually names its weights with --pretrained_checkpoint)
+            where = args.load or args.pretrained_checkpoint
+            assert where is not None, "predictions need --load or --pretrained_checkpoint to be written to"
+            torch.save(named, os.path.join(where, "predictions.pt"))
     return metrics_func
 
 

@@ -137,7 +137,10 @@ def finetune(train_valid_datasets_provider, model_provider, model_type=ModelType
         train_ds, valid_ds = train_valid_datasets_provider()
         train_dl, valid_dl = _build_train_valid_dataloaders(train_ds, valid_ds, task_collate_fn)
     else:
+        # evaluation only (--epochs 0): the metric callbacks size their loaders from the batch sizes the
+        # user gave, which the training branch records while it builds its loaders
         args.train_iters = 0
+        args.orig_micro_batch_size, args.orig_global_batch_size = args.micro_batch_size, args.global_batch_size
         train_dl = valid_dl = None
     timers("train/valid/test dataset/dataloder").stop()
     callback = end_of_epoch_callback_provider() if end_of_epoch_callback_provider is not None else None

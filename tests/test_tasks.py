@@ -371,3 +371,50 @@ def test_msdp_prompt_cli_generates_one_line_per_sample(tmp_path, prompt_type):
     lines = open(tmp_path / "out.txt").read().split("\n")
     assert len(lines) == len(samples) + 1 and lines[-1] == ""
     assert all(len(ln) <= 8 for ln in lines)        # at most --out_seq_length single-character tokens
+
+
+def test_qqp_finetune_then_evaluation_only(tmp_path):
+    """tasks/main.py --task QQP: one finetuning epoch with a checkpoint at the end, then an evaluation-only
+    run (--epochs 0 --pretrained_checkpoint) of the saved weights: same accuracy line, predictions written
+    next to the checkpoint."""
+    import re
+    import torch
+    words = "the of and to in a is that for it as was with be by on not he this are".split()
+    (tmp_path / "vocab.txt").write_text("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]"] + words) + "\n")
+    rng = np.random.RandomState(0)
+
+    def tsv(path, n):
+        rows = ["id\tqid1\tqid2\tquestion1\tquestion2\tis_duplicate"]
+        for i in range(n):
+            rows.append("\t".join([str(i), str(2 * i), str(2 * i + 1), " ".join(rng.choice(words, 6)),
+                                   " ".join(rng.choice(words, 5)), str(i % 2)]))
+        path.write_text("\n".join(rows) + "\n")
+    tsv(tmp_path / "train.tsv", 24)
+    tsv(tmp_path / "dev.tsv", 8)
+
+    def run(extra):
+        env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1",
+                   B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+        cmd = [sys.executable, os.path.join(ROOT, "tasks", "main.py"), "--task", "QQP",
+               "--train_data", str(tmp_path / "train.tsv"), "--valid_data", str(tmp_path / "dev.tsv"),
+               "--tokenizer_type", "BertWordPieceLowerCase", "--vocab_file", str(tmp_path / "vocab.txt"),
+               "--num_layers", "2", "--hidden_size", "32", "--num_attention_heads", "2", "--seq_length", "32",
+               "--max_position_embeddings", "32", "--micro_batch_size", "4", "--global_batch_size", "4",
+               "--lr", "1e-3", "--lr_decay_style", "linear", "--lr_warmup_fraction", "0.1",
+               "--distributed_backend", "gloo", "--use_cpu_initialization", "--no_bias_gelu_fusion",
+               "--no_masked_softmax_fusion", "--num_workers", "0", "--log_interval", "2", "--eval_interval", "100",
+               "--eval_iters", "1", "--make_vocab_size_divisible_by", "8", "--hidden_dropout", "0.0",
+               "--attention_dropout", "0.0"] + extra
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+        assert "done :-)" in r.stdout
+        return re.search(r"overall: correct / total = (\d+) / (\d+)", r.stdout).groups()
+
+    trained = run(["--epochs", "1", "--save", str(tmp_path / "ck"), "--save_interval", "100"])
+    assert trained[1] == "8"
+    assert open(tmp_path / "ck" / "latest_checkpointed_iteration.txt").read().strip() == "6"
+    evaluated = run(["--epochs", "0", "--pretrained_checkpoint", str(tmp_path / "ck")])
+    assert evaluated == trained
+    preds = torch.load(tmp_path / "ck" / "predictions.pt", weights_only=False)
+    (name, (softmaxes, labels, ids)), = preds.items()
+    assert len(labels) == 8 and len(ids) == 8 and np.asarray(softmaxes).shape == (8, 2)

@@ -18,6 +18,9 @@ class HeadedModel(MegatronModule):
     {language_model: ..., <key>: head.state_dict(), [word_embeddings_for_head: ...]}."""
     _language_model_key = "language_model"
     _head_keys: dict = {}
+    # task heads put on top of a pretrained model start from random weights when the checkpoint has
+    # none (megatron/model/classification.py:97-108); pretraining heads must be in the checkpoint
+    _heads_may_be_missing = False
 
     def set_input_tensor(self, input_tensor):
         self.language_model.set_input_tensor(input_tensor)
@@ -45,9 +48,11 @@ class HeadedModel(MegatronModule):
                 mod = getattr(self, attr, None)
                 if mod is not None and key in state_dict:
                     mod.load_state_dict(state_dict[key], strict=strict)
-                elif mod is not None:
+                elif mod is not None and self._heads_may_be_missing:
                     print(f"***WARNING*** could not find {key} in the checkpoint, initializing to random",
                           flush=True)
+                elif mod is not None:
+                    raise KeyError(f"{key} is missing from the checkpoint")
         if self._ties_embeddings_on_last_stage() and self.post_process and not self.pre_process:
             self.word_embeddings.load_state_dict(state_dict[self._word_embeddings_for_head_key], strict=strict)
 

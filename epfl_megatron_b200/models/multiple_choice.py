@@ -13,6 +13,7 @@ from .utils import get_linear_layer, init_method_normal, scaled_init_method_norm
 
 class MultipleChoice(HeadedModel):
     _head_keys = {"multichoice_head": "multichoice_head"}
+    _heads_may_be_missing = True
 
     def __init__(self, num_tokentypes=2, pre_process=True, post_process=True):
         super().__init__(share_word_embeddings=False)

@@ -95,3 +95,62 @@ def test_t5_encoder_decoder_pipeline_split(tmp_path, stages, split, layers):
     losses = [float(x) for x in re.findall(r"\| lm loss: ([0-9.E+-]+)", r.stdout)]
     assert len(losses) >= 3 and losses[-1] < losses[0], r.stdout[-1500:]
     assert "validation loss at iteration 2" in r.stdout
+
+
+def test_bert_checkpoint_reshards_with_its_heads(tmp_path):
+    """tools/checkpoint_util.py --model_type BERT carries the masked-LM head (its bias is vocabulary
+    parallel), the binary head and the pooler: continuing from the TP2 reshard on two ranks starts from
+    the same losses as continuing from the original on one rank. A BERT checkpoint without its heads is
+    refused instead of silently training re-initialised ones."""
+    import re
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tests", "helpers"))
+    try:
+        import legacy_worker
+    finally:
+        sys.path.pop(0)
+    vf, prefix, _ = legacy_worker.make_corpus(str(tmp_path))
+
+    def run(nproc, extra, expect_ok=True):
+        argv = (f"--num_layers 2 --hidden_size 64 --num_attention_heads 4 --seq_length 48 --max_position_embeddings 64 "
+                f"--micro_batch_size 2 --global_batch_size 4 --lr 2e-3 --min_lr 1e-4 --lr_decay_style constant "
+                f"--tokenizer_type BertWordPieceLowerCase --vocab_file {vf} --data_path {prefix} --split 90,5,5 "
+                f"--distributed_backend gloo --use_cpu_initialization --hidden_dropout 0.0 --attention_dropout 0.0 "
+                f"--no_bias_gelu_fusion --no_masked_softmax_fusion --num_workers 0 --eval_iters 1 --eval_interval 100 "
+                f"--log_interval 1 --make_vocab_size_divisible_by 8 --data_impl mmap --seed 7 " + extra).split()
+        env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), B200_DISABLE_KERNELS="1",
+                   CUDA_VISIBLE_DEVICES="")
+        if nproc == 1:
+            env.update(RANK="0", WORLD_SIZE="1", LOCAL_RANK="0")
+            cmd = [sys.executable, os.path.join(ROOT, "pretrain_bert.py")]
+        else:
+            cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+                   "--master-addr", "127.0.0.1", "--master-port", env["MASTER_PORT"],
+                   os.path.join(ROOT, "pretrain_bert.py")]
+        r = subprocess.run(cmd + argv, capture_output=True, text=True, timeout=900, env=env, cwd=ROOT)
+        if not expect_ok:
+            return r
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3500:]
+        return [(float(a), float(b)) for a, b in
+                re.findall(r"lm loss: ([0-9.E+-]+) \| sop loss: ([0-9.E+-]+)", r.stdout)]
+
+    run(1, f"--train_iters 3 --save {tmp_path / 'ck'} --save_interval 3")
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", B200_DISABLE_KERNELS="1")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "checkpoint_util.py"), "--model_type", "BERT",
+                        "--load_dir", str(tmp_path / "ck"), "--save_dir", str(tmp_path / "ck_tp2"),
+                        "--target_tensor_parallel_size", "2", "--target_pipeline_parallel_size", "1"],
+                       capture_output=True, text=True, cwd=ROOT, env=env)
+    assert r.returncode == 0, r.stderr[-3000:]
+    one = run(1, f"--train_iters 2 --finetune --load {tmp_path / 'ck'}")
+    two = run(2, f"--train_iters 2 --finetune --load {tmp_path / 'ck_tp2'} --tensor_model_parallel_size 2")
+    assert len(one) == len(two) == 2
+    for (a_lm, a_sop), (b_lm, b_sop) in zip(one, two):
+        assert abs(a_lm - b_lm) <= 1e-4 * a_lm and abs(a_sop - b_sop) <= 1e-4 * abs(a_sop), (one, two)
+    # strip the heads from a copy of the original: loading must fail loudly
+    import megatron  # noqa: F401
+    path = tmp_path / "ck" / "iter_0000003" / "mp_rank_00" / "model_optim_rng.pt"
+    sd = torch.load(path, map_location="cpu", weights_only=False)
+    del sd["model"]["lm_head"]
+    torch.save(sd, path)
+    bad = run(1, f"--train_iters 2 --finetune --load {tmp_path / 'ck'}", expect_ok=False)
+    assert bad.returncode != 0 and "lm_head is missing from the checkpoint" in bad.stderr

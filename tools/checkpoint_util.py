@@ -94,6 +94,15 @@ def load_full(load_dir):
                 full["lm_head"] = torch.cat([lm["lm_head"] for lm in lms], dim=0)
             if "pooler" in lms[0]:
                 full["pooler"] = lms[0]["pooler"]
+            # task heads next to the language model (BERT: lm_head, binary_head; classification /
+            # multiple-choice heads): replicated over TP except the vocabulary-parallel lm_head bias
+            for name, sub_d in shards[0][ck].items():
+                if name in ("language_model", "word_embeddings_for_head") or not isinstance(sub_d, dict):
+                    continue
+                full.setdefault("heads", OrderedDict())[name] = OrderedDict(
+                    (leaf, torch.cat([s[ck][name][leaf] for s in shards], dim=0)
+                     if (name, leaf) == ("lm_head", "bias") else val.clone())
+                    for leaf, val in sub_d.items() if torch.is_tensor(val))
     return full, a, it
 
 
@@ -142,6 +151,14 @@ def save_sharded(full, src_args, iteration, save_dir, tp, pp, true_vocab_size=No
             if p == pp - 1 and "pooler" in full:
                 lm["pooler"] = full["pooler"]
             model = {"language_model": lm}
+            if p == pp - 1:
+                for name, sub_d in full.get("heads", {}).items():
+                    model[name] = OrderedDict()
+                    for leaf, val in sub_d.items():
+                        if (name, leaf) == ("lm_head", "bias"):
+                            val = torch.cat([val[:true_v], val.new_zeros(max(new_v - true_v, 0))])[:new_v]
+                            val = val.chunk(tp, dim=0)[t]
+                        model[name][leaf] = val.clone()
             if tied and pp > 1 and p == pp - 1:
                 model["word_embeddings_for_head"] = OrderedDict(weight=emb_split[t].clone())
             out = os.path.join(save_dir, sub, _rank_dir(t, p, pp))

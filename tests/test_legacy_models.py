@@ -146,6 +146,34 @@ def test_bert_checkpoint_reshards_with_its_heads(tmp_path):
     assert len(one) == len(two) == 2
     for (a_lm, a_sop), (b_lm, b_sop) in zip(one, two):
         assert abs(a_lm - b_lm) <= 1e-4 * a_lm and abs(a_sop - b_sop) <= 1e-4 * abs(a_sop), (one, two)
+    # the loader -> saver plug-in protocol writes the same shards, heads and pooler included
+    import queue as pyqueue
+    import types
+    sys.path.insert(0, ROOT)
+    from tools import checkpoint_loader_megatron as loader, checkpoint_saver_megatron as saver
+    q = pyqueue.Queue()
+    a = types.SimpleNamespace(model_type="BERT", load_dir=str(tmp_path / "ck"), save_dir=str(tmp_path / "ck_queue"),
+                              checking=True, true_vocab_size=None, target_tensor_parallel_size=2,
+                              target_pipeline_parallel_size=1)
+    loader.load_checkpoint(q, a)
+    saver.save_checkpoint(q, a)
+
+    def flat(x, pre=""):
+        out = {}
+        for k, val in x.items():
+            if isinstance(val, dict):
+                out.update(flat(val, pre + k + "/"))
+            elif torch.is_tensor(val):
+                out[pre + k] = val
+        return out
+    for t in range(2):
+        d = flat(torch.load(tmp_path / "ck_tp2" / "iter_0000003" / f"mp_rank_{t:02d}" / "model_optim_rng.pt",
+                            weights_only=False)["model"])
+        v = flat(torch.load(tmp_path / "ck_queue" / "iter_0000003" / f"mp_rank_{t:02d}" / "model_optim_rng.pt",
+                            weights_only=False)["model"])
+        assert d.keys() == v.keys() and {"lm_head/bias", "binary_head/weight", "language_model/pooler/dense.weight",
+                                         "language_model/embedding/tokentype_embeddings/weight"} <= d.keys(), sorted(d)
+        assert all(torch.equal(d[k], v[k]) for k in d)
     # strip the heads from a copy of the original: loading must fail loudly
     import megatron  # noqa: F401
     path = tmp_path / "ck" / "iter_0000003" / "mp_rank_00" / "model_optim_rng.pt"

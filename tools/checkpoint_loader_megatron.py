@@ -52,6 +52,8 @@ def _load_checkpoint(queue, args):
     msg = {"word embeddings": emb["word_embeddings"]["weight"]}
     if "position_embeddings" in emb:
         msg["position embeddings"] = emb["position_embeddings"]["weight"]
+    if "tokentype_embeddings" in emb:
+        msg["tokentype embeddings"] = emb["tokentype_embeddings"]["weight"]
     send("embeddings", msg)
     enc = full["encoder"]
     n_layers = 1 + max((layer_index(k)[0] for k in enc if layer_index(k)[0] is not None), default=-1)
@@ -62,6 +64,10 @@ def _load_checkpoint(queue, args):
                              if k.startswith("final_layernorm.")})
     if "lm_head" in full:
         send("lm_head", {"lm_head": full["lm_head"]})
+    if "pooler" in full:
+        send("pooler", dict(full["pooler"]))
+    for name, sub_d in full.get("heads", {}).items():      # BERT: "lm_head" (module), "binary_head"
+        send(f"head {name}", dict(sub_d))
     queue.put("done")
 
 

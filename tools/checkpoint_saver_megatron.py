@@ -49,6 +49,8 @@ def save_checkpoint(queue, args):
     full["embedding"] = OrderedDict(word_embeddings=OrderedDict(weight=emb["word embeddings"]))
     if "position embeddings" in emb:
         full["embedding"]["position_embeddings"] = OrderedDict(weight=emb["position embeddings"])
+    if "tokentype embeddings" in emb:
+        full["embedding"]["tokentype_embeddings"] = OrderedDict(weight=emb["tokentype embeddings"])
     enc = OrderedDict()
     for i in range(md.num_layers):
         msg = queue_get(f"transformer layer {i}")
@@ -62,11 +64,18 @@ def save_checkpoint(queue, args):
             enc[f"final_layernorm.{k}"] = v
     full["encoder"] = enc
     msg = queue_get()
-    if msg != "done" and msg.get("name") == "lm_head":
-        full["lm_head"] = msg["lm_head"]
+    while msg != "done":
+        name = msg.pop("name", None)
+        if name == "lm_head":
+            full["lm_head"] = msg["lm_head"]
+        elif name == "pooler":
+            full["pooler"] = OrderedDict(msg)
+        elif name is not None and name.startswith("head "):
+            full.setdefault("heads", OrderedDict())[name[len("head "):]] = OrderedDict(msg)
+        else:
+            print(f"ERROR: unexpected message {name!r}; was expecting to be done")
+            break
         msg = queue_get()
-    if msg != "done":
-        print("ERROR: got some more data but was expecting to be done")
     true_vocab = getattr(args, "true_vocab_size", None) or getattr(md, "true_vocab_size", None)
     save_sharded(full, md.checkpoint_args, md.iteration, args.save_dir, tp, pp, true_vocab)
     print(f"Done! saved tp={tp} pp={pp} checkpoint to {args.save_dir}")

@@ -117,3 +117,24 @@ def test_gpt_tied_embeddings_on_four_pipeline_stages(tmp_path):
     middle = torch.load(tmp_path / "ck" / "iter_0000003" / "mp_rank_00_001" / "model_optim_rng.pt",
                         map_location="cpu", weights_only=False)["model"]
     assert "word_embeddings_for_head" not in middle and "embedding" not in middle["language_model"]
+
+
+def test_interleaved_pipeline_checkpoint_unshards_to_one_rank(tmp_path):
+    """A checkpoint written by the interleaved schedule (two stages x two model chunks, tied embeddings)
+    goes back to tp 1 x pp 1 through tools/checkpoint_util.py with the layers in their global order:
+    the one-rank test loss equals the one the pipeline run reported for the same weights."""
+    import subprocess
+    import sys
+    from tests.helpers.launch import ROOT
+    from tests.test_cli_e2e_cpu import _corpus
+    _corpus(str(tmp_path / "corpus"))
+    trained = _gpt_cli(tmp_path, 2, ["--save", str(tmp_path / "ck"), "--save_interval", "3",
+                                     "--num_layers_per_virtual_pipeline_stage", "1"], pp=2)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "checkpoint_util.py"), "--model_type", "GPT",
+                        "--load_dir", str(tmp_path / "ck"), "--save_dir", str(tmp_path / "ck11"),
+                        "--target_tensor_parallel_size", "1", "--target_pipeline_parallel_size", "1"],
+                       capture_output=True, text=True, cwd=ROOT, env=dict(os.environ, **ENV))
+    assert r.returncode == 0, r.stderr[-3000:]
+    single = _gpt_cli(tmp_path, 1, ["--load", str(tmp_path / "ck11"), "--no_load_optim", "--no_load_rng"])
+    assert "at iteration 3" in single
+    assert abs(_test_loss(single) - _test_loss(trained)) <= 2e-5 * _test_loss(trained)

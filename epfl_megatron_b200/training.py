@@ -622,6 +622,14 @@ def build_train_valid_test_data_iterators(build_train_valid_test_datasets_provid
     def mk(dl):
         if dl is None:
             return None
-        return iter(dl) if dl_type == "single" else iter(cyclic_iter(dl))
+        if dl_type != "single":
+            return iter(cyclic_iter(dl))
+        # a DataLoader iterator draws its base seed from the default generator when it is created; keep
+        # the model's random stream (CPU dropout) independent of it, so that a resumed run, which builds
+        # its iterators after the checkpoint's generator state was restored, replays the same numbers
+        state = torch.get_rng_state()
+        it = iter(dl)
+        torch.set_rng_state(state)
+        return it
 
     return mk(train_dl), mk(valid_dl), mk(test_dl)

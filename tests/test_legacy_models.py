@@ -182,3 +182,40 @@ def test_bert_checkpoint_reshards_with_its_heads(tmp_path):
     torch.save(sd, path)
     bad = run(1, f"--train_iters 2 --finetune --load {tmp_path / 'ck'}", expect_ok=False)
     assert bad.returncode != 0 and "lm_head is missing from the checkpoint" in bad.stderr
+
+
+@pytest.mark.parametrize("script,extra", [
+    ("pretrain_bert.py", ""),
+    ("pretrain_t5.py", "--decoder_seq_length 32 --vocab_extra_ids 100 --kv_channels 16 --ffn_hidden_size 128 "),
+])
+def test_legacy_resume_replays_dropout(tmp_path, script, extra):
+    """Save after two of four iterations (--exit_interval), resume in a new process: with dropout ON the
+    loss curve equals the uninterrupted run digit for digit -- generator states, data position and
+    optimizer state all come back (the data-loader iterators do not disturb the restored generator)."""
+    import re
+    sys.path.insert(0, os.path.join(ROOT, "tests", "helpers"))
+    try:
+        import legacy_worker
+    finally:
+        sys.path.pop(0)
+    vf, prefix, _ = legacy_worker.make_corpus(str(tmp_path))
+
+    def run(more):
+        argv = (f"--num_layers 2 --hidden_size 64 --num_attention_heads 4 --seq_length 48 --max_position_embeddings 64 "
+                f"--micro_batch_size 2 --global_batch_size 4 --lr 2e-3 --min_lr 1e-4 --train_iters 4 "
+                f"--lr_decay_style constant --tokenizer_type BertWordPieceLowerCase --vocab_file {vf} "
+                f"--data_path {prefix} --split 90,5,5 --distributed_backend gloo --use_cpu_initialization "
+                f"--hidden_dropout 0.1 --attention_dropout 0.1 --no_bias_gelu_fusion --no_masked_softmax_fusion "
+                f"--num_workers 0 --eval_iters 1 --eval_interval 100 --log_interval 1 "
+                f"--make_vocab_size_divisible_by 8 --data_impl mmap --seed 7 " + extra + more).split()
+        env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(free_port()), RANK="0", WORLD_SIZE="1",
+                   LOCAL_RANK="0", B200_DISABLE_KERNELS="1", CUDA_VISIBLE_DEVICES="")
+        r = subprocess.run([sys.executable, os.path.join(ROOT, script)] + argv, capture_output=True, text=True,
+                           timeout=900, env=env, cwd=ROOT)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3500:]
+        return re.findall(r"lm loss: ([0-9.E+-]+)", r.stdout)
+
+    whole = run("")
+    first = run(f"--save {tmp_path / 'ck'} --save_interval 2 --exit_interval 2")
+    second = run(f"--load {tmp_path / 'ck'}")
+    assert len(whole) == 4 and first == whole[:2] and second == whole[2:], (whole, first, second)

@@ -23,7 +23,8 @@ def rmsnorm(x, weight, eps):
     """fp32 x*rsqrt(mean(x^2)+eps), cast back, THEN scale (model/fused_layer_norm.py:125-139)."""
     xf = x.float()
     y = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
-    return (y.type_as(x) * weight).to(_norm_out_dtype(x, weight))
+    out = y.type_as(x) * weight
+    return out.to(weight.dtype) if _norm_out_dtype(x, weight) != x.dtype else out
 
 
 def layernorm(x, weight, bias, eps):

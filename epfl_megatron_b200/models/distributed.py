@@ -97,6 +97,10 @@ class DistributedDataParallel(DistributedDataParallelBase):
         self._reduced = False
         self.bucket_bytes = int(bucket_mb * (1 << 20))
         self._buckets, self._bucket_of, self._arrivals, self._expected = [], {}, {}, 0
+        # gradient contributions a parameter receives per micro-batch (1 for most; 2 for a word
+        # embedding that is also the LM head: lookup gradient through the autograd hook + the
+        # head's weight-gradient epilogue; 3 for T5's shared table). Measured on the first step.
+        self._uses, self._calibrating = None, False
         self._handles = []
         self.accumulate_allreduce_grads_in_fp32 = accumulate_allreduce_grads_in_fp32
         self.use_contiguous_buffers = use_contiguous_buffers
@@ -240,9 +244,17 @@ class DistributedDataParallel(DistributedDataParallelBase):
             return
         n = self._arrivals.get(p, 0) + 1
         self._arrivals[p] = n
-        if n != self._expected:
+        if self._calibrating:
             return
         b = self._bucket_of[p]
+        target = self._uses.get(p, 0) * self._expected
+        if b.launched or (target and n > target):
+            raise RuntimeError(
+                "a gradient contribution arrived after its bucket's data-parallel reduction was launched "
+                f"(arrival {n}, expected {target}): the parameter is used a different number of times "
+                "per micro-batch than on the first step; run with --no_overlap_grad_reduce")
+        if n != target:
+            return
         b.pending -= 1
         if b.pending == 0 and b.early_ok and not b.launched and self.overlap_grad_reduce:
             self._launch(b, async_op=True)
@@ -276,6 +288,15 @@ class DistributedDataParallel(DistributedDataParallelBase):
         then skips its own reduction), False when overlap is off."""
         if not self._expected:
             return self._reduced
+        if self._calibrating:
+            # first step: nothing was launched early; learn how often each parameter is written
+            self._uses = {}
+            for p, n in self._arrivals.items():
+                if n % self._expected == 0:
+                    self._uses[p] = n // self._expected
+                else:
+                    self._bucket_of[p].early_ok = False
+            self._calibrating = False
         for b in self._buckets:
             if not b.launched:
                 self._launch(b, async_op=False)
@@ -300,6 +321,7 @@ class DistributedDataParallel(DistributedDataParallelBase):
             from .. import global_vars
             self._expected = global_vars.get_num_microbatches()
             self._arrivals = {}
+            self._calibrating = self._uses is None
             for b in self._buckets:
                 b.pending, b.launched = len(b.params), False
             for ws in self._dp_ws.values():

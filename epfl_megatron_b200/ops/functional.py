@@ -29,6 +29,9 @@ def set_gemm_mode(mode: str):
     _GEMM_MODE = mode
 
 
+_HOST_FUSED_WGRAD = os.environ.get("B200_HOST_FUSED_WGRAD", "0") == "1"
+
+
 def kernels_enabled() -> bool:
     return _MODE != "off" and L.available()
 
@@ -524,7 +527,16 @@ def gemm_nn(dy2d, w, force_own=False):
 
 def wgrad_accumulate(dy2d, x2d, main_grad, accumulate=True):
     """main_grad[N,K] (fp32) (+)= dy2d[M,N]^T @ x2d[M,K] in ONE kernel (N5 equivalent).
-    Returns False when the fused kernel cannot be used (caller falls back)."""
+    Returns False when the fused kernel cannot be used (caller falls back).
+    B200_HOST_FUSED_WGRAD=1 restates the epilogue with torch on tensors the kernel does not take
+    (CPU / fp32), so the arrival order it creates -- gradient written outside autograd, then
+    ``_b200_grad_ready`` -- can be exercised on Gloo."""
+    if _HOST_FUSED_WGRAD and not _k(dy2d) and main_grad.dtype == torch.float32:
+        if accumulate:
+            main_grad.addmm_(dy2d.t().float(), x2d.float())
+        else:
+            torch.mm(dy2d.t().float(), x2d.float(), out=main_grad)
+        return True
     if _GEMM_MODE == "cublas" or not _own_gemm_ok(dy2d, x2d) or main_grad.dtype != torch.float32 \
             or not main_grad.is_contiguous():
         return False

@@ -49,6 +49,20 @@ def test_dp2_fused_reduce_scatter_and_param_push():
     _close(fused["grad_norms"], nccl["grad_norms"], 5e-3)
 
 
+def test_dp2_tied_gpt_overlap_matches_no_overlap():
+    """Tied embeddings at pp = 1: the embedding gradient arrives twice per micro-batch (LM-head
+    weight-gradient epilogue + lookup). Overlapped bucket reduction (NCCL and the fused path) must
+    equal one reduction after backward; replicas stay identical (checksum check every step)."""
+    _need(2)
+    kw = dict(nproc=2, steps=5, model_name="gpt", dist_opt=True, num_microbatches=2, bucket_mb=1, layers=2,
+              check_dp=1)
+    ref = run_tiny(no_overlap=True, fused_dp="off", **kw)
+    for mode in ("off", "on"):
+        got = run_tiny(fused_dp=mode, **kw)
+        _close(got["losses"], ref["losses"], 2e-3)
+        _close(got["grad_norms"], ref["grad_norms"], 5e-3)
+
+
 def test_dp4_fused_with_tp2():
     _need(8)
     kw = dict(nproc=8, tp=2, steps=5, dist_opt=True, num_microbatches=2, bucket_mb=1, layers=4)

@@ -44,6 +44,23 @@ def test_dp2_overlapped_bucketed_grad_reduce_matches_single_reduce():
         _close(got, ref, 1e-5)
 
 
+def test_dp2_tied_embeddings_overlap_counts_every_use():
+    """A tied GPT (word embedding == LM head, pp = 1) writes the embedding gradient twice per
+    micro-batch: the head's weight-gradient epilogue (outside autograd) and the lookup gradient
+    (autograd hook). The bucket holding it must not be reduced before both have landed in the last
+    micro-batch: overlapped == one reduction after backward, with the weight-gradient epilogue
+    restated on the host so the arrival order is the GPU's."""
+    kw = dict(KW, model_name="gpt", num_microbatches=2, layers=2, steps=4)
+    env = dict(ENV, B200_HOST_FUSED_WGRAD="1")
+    ref = run_tiny(nproc=2, no_overlap=True, env_extra=env, **kw)
+    for extra in (dict(bucket_mb=0), dict(bucket_mb=0, dist_opt=True), dict(bucket_mb=0, num_microbatches=1)):
+        k2 = dict(kw, **extra)
+        want = ref if "num_microbatches" not in extra else run_tiny(nproc=2, no_overlap=True, env_extra=env, **k2)
+        got = run_tiny(nproc=2, env_extra=env, **k2)
+        _close(got["losses"], want["losses"], 1e-5)
+        _close(got["grad_norms"], want["grad_norms"], 1e-5)
+
+
 def test_dp2_ddp_impl_torch_matches_local():
     """--DDP_impl torch (parameter-dtype gradients averaged in 25 MiB buckets during backward) trains
     like --DDP_impl local with one reduction after backward."""

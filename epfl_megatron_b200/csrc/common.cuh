@@ -6,6 +6,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cstdio>
 #include <cuda_fp16.h>
 #include <cuda.h>
 #include <stdint.h>

@@ -13,8 +13,9 @@
 //                      (16-byte peer stores): the all-gather is the kernel's own epilogue.
 //
 // Flags are monotonic step numbers written with st.release.sys by the producer and polled with
-// ld.acquire.sys; waits are bounded and record {site, value, target, index} in g_dp_debug instead of
-// hanging the device.
+// ld.acquire.sys; waits are bounded (about a minute): a timed-out wait records {site, value, target,
+// index} in g_dp_debug, prints one line and traps, so a lost peer ends the job with a launch error
+// instead of a hung device or a step computed from half-reduced gradients.
 #include "common.cuh"
 
 namespace b200 {
@@ -37,14 +38,17 @@ __device__ __forceinline__ void dp_spin(const unsigned* p, unsigned target, unsi
     asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     if (static_cast<int>(v - target) >= 0) return;
     __nanosleep(256);
-    if (clock64() - t0 > 20000000000LL) {
+    if (clock64() - t0 > 120000000000LL) {
       if (atomicCAS(&g_dp_debug[0], 0u, site) == 0u) {
         g_dp_debug[1] = v;
         g_dp_debug[2] = target;
         g_dp_debug[3] = index;
         g_dp_debug[4] = blockIdx.x;
+        __threadfence_system();
+        printf("b200 fused DP path: wait timed out (site %u, cta %u, saw %u, wanted %u, index %u)\n", site,
+               blockIdx.x, v, target, index);
       }
-      return;
+      asm volatile("trap;");
     }
   }
 }

@@ -21,8 +21,10 @@
 //     strip's counters show all tp contributions.
 //
 // Protocol state lives in the symmetric workspace (csrc/comm.cu): monotonic u32 counters
-// compared with wrap-around arithmetic, one epoch per call. Waits on other GPUs are bounded
-// (trap after ~5 s) so a protocol bug surfaces as a launch error instead of a hung device.
+// compared with wrap-around arithmetic, one epoch per call. Waits on other GPUs are bounded:
+// after kWaitLimitCycles (about a minute, far above any host-side launch skew between ranks) the
+// wait is recorded, printed and the kernel traps, so a lost peer or a protocol bug ends the job
+// with a launch error instead of a hung device or a silently wrong step.
 // The MMA pipeline is the CTA-pair kernel of gemm_tcgen05.cu (cta_group::2, 256 x 256 tiles).
 #include "common.cuh"
 
@@ -92,9 +94,12 @@ __device__ __forceinline__ bool reached(unsigned v, unsigned target) {
   return static_cast<int>(v - target) >= 0;
 }
 // First wait that timed out: {site, blockIdx, value seen, target, epoch, mode, rank, index}.
-// A timed-out wait is recorded and then abandoned (the result of that call is garbage, the host
-// checks b200_comm_debug_read in debug / test runs); the GPU is never left spinning.
+// A timed-out wait is fatal: the record below is kept for b200_comm_debug_read (readable while the
+// context is alive, i.e. by other streams' checks before the error surfaces), one line is printed
+// and the kernel traps like csrc/comm.cu's waits do. Continuing with a partially gathered or
+// partially reduced tile would train on garbage.
 __device__ unsigned g_comm_debug[8];
+constexpr long long kWaitLimitCycles = 120000000000LL;   // ~60 s at 1.97 GHz, ~80 s under a power cap
 
 template <bool kSys>
 __device__ __forceinline__ void spin_until(const unsigned* p, unsigned target, unsigned site,
@@ -103,7 +108,7 @@ __device__ __forceinline__ void spin_until(const unsigned* p, unsigned target, u
   unsigned v;
   while (!reached(v = (kSys ? ld_acquire_sys(p) : ld_acquire_gpu(p)), target)) {
     __nanosleep(64);
-    if (clock64() - t0 > 4000000000LL) {
+    if (clock64() - t0 > kWaitLimitCycles) {
       if (atomicCAS(&g_comm_debug[0], 0u, site) == 0u) {
         g_comm_debug[1] = blockIdx.x;
         g_comm_debug[2] = v;
@@ -112,8 +117,11 @@ __device__ __forceinline__ void spin_until(const unsigned* p, unsigned target, u
         g_comm_debug[5] = (unsigned)mode;
         g_comm_debug[6] = (unsigned)rank;
         g_comm_debug[7] = index;
+        __threadfence_system();
+        printf("b200 fused TP collective: wait timed out (site %u, rank %d, cta %u, saw %u, wanted %u, "
+               "epoch %u, mode %d, index %u)\n", site, rank, blockIdx.x, v, target, epoch, mode, index);
       }
-      return;
+      asm volatile("trap;");
     }
   }
 }

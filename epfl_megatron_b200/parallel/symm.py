@@ -209,6 +209,9 @@ def get_workspace(group, max_rows, max_k, max_n):
     if ws is None or ws.max_rows < max_rows or ws.max_k < max_k or ws.max_n < max_n:
         if ws is not None:
             max_rows, max_k, max_n = max(max_rows, ws.max_rows), max(max_k, ws.max_k), max(max_n, ws.max_n)
+            # every GPU of the group must have drained its kernels (they read and write the peers'
+            # buffers) BEFORE anybody unmaps or frees: device sync first, then the host barrier
+            torch.cuda.synchronize()
             dist.barrier(group=group)
             ws.close()
         ws = _WORKSPACE = TPWorkspace(group, max_rows, max_k, max_n)

@@ -69,17 +69,41 @@ def _one_case(lib, M, H, seed, with_dres, accumulate):
     dx, dw = torch.empty_like(x), dw0.clone()
     torch.cuda.synchronize()
     before = torch.cuda.memory_allocated()
+    # the driver's own count of free bytes sees a cudaMalloc inside the library, which torch's
+    # allocator statistics would not (the one-time symbol look-up of the first call on a device
+    # happened in _warm_up, before this snapshot)
+    free_before = torch.cuda.mem_get_info()[0]
     rc = lib.b200_rmsnorm_bwd_noalloc(dy.data_ptr(), x.data_ptr(), w.data_ptr(), rstd.data_ptr(), dp,
                                       dx.data_ptr(), dw.data_ptr(), M, H, int(accumulate), stream)
     assert rc == 0, f"b200_rmsnorm_bwd_noalloc returned {rc}"
     torch.cuda.synchronize()
     assert torch.cuda.memory_allocated() == before
+    assert torch.cuda.mem_get_info()[0] >= free_before, "device memory was taken during the call"
     _close(dx, dx_ref, 2e-2, 2e-2, f"dx M={M} H={H}")
-    _close(dw, dw_ref, 0.5, 2e-2, f"dw M={M} H={H}")
+    # dw: both entry points sum the same fp32 partial rows in the same order; against the fp32
+    # restatement the error is rounding only, so a dropped partial row (1/grid of the sum) shows
+    dw_fp32 = dw0 + (dy.float() * (x.float() * rstd[:, None]).bfloat16().float()).sum(0)
+    scale = float(dw_fp32.abs().max())
+    _close(dw, dw_ref, 1e-4 * scale, 1e-4, f"dw vs regular entry point M={M} H={H}")
+    _close(dw, dw_fp32, 2e-3 * scale, 2e-3, f"dw vs fp32 restatement M={M} H={H}")
+
+
+def _warm_up(lib):
+    """First call on this device: the entry point looks up the address of its array (documented:
+    make this call outside any stream capture)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
+    t = torch.zeros(8, 256, device=dev).bfloat16()
+    r = torch.ones(8, device=dev)
+    o, dw = torch.empty_like(t), torch.zeros(256, device=dev)
+    assert lib.b200_rmsnorm_bwd_noalloc(t.data_ptr(), t.data_ptr(), t[0].data_ptr(), r.data_ptr(), None,
+                                        o.data_ptr(), dw.data_ptr(), 8, 256, 0,
+                                        torch.cuda.current_stream().cuda_stream) == 0
+    torch.cuda.synchronize()
 
 
 def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     lib = _load()
+    _warm_up(lib)
     # first call: tall input, all 148 partial rows get written
     _one_case(lib, M=2048, H=4096, seed=1, with_dres=False, accumulate=False)
     # second call straight after it: fewer rows than CTAs and a wider H, so the array still

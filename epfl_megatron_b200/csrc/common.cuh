@@ -90,6 +90,14 @@ __device__ __forceinline__ void unpack8(const bf16x8& p, float* f) {
     f[2 * i + 1] = t.y;
   }
 }
+__device__ __forceinline__ void unpack8(const uint4& q, float* f) {
+  const uint32_t u[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(u[i] << 16);
+    f[2 * i + 1] = __uint_as_float(u[i] & 0xFFFF0000u);
+  }
+}
 __device__ __forceinline__ bf16x8 pack8(const float* f) {
   bf16x8 p;
 #pragma unroll

@@ -13,6 +13,7 @@
 // registers across all of that CTA's rows and written once to a [grid, H] fp32
 // scratch; a second tiny kernel folds the scratch into the (optionally accumulated)
 // fp32 gradient.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b200 {
@@ -293,6 +294,24 @@ void rmsnorm_bwd_warp(const void* dy, const void* x, const void* w, const float*
                       void* dx, float* dw, float* scratch, int max_strips, int M, int H, int accumulate,
                       cudaStream_t stream);
 
+bool rmsnorm_tma_ok(int M, int H);
+int rmsnorm_fwd_tma(const void* x, const void* residual, const void* w, void* y, void* h_out,
+                    float* rstd, int M, int H, float eps, cudaStream_t stream);
+int rmsnorm_bwd_tma(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                    void* dx, float* dw, float* scratch, int M, int H, int accumulate,
+                    cudaStream_t stream);
+
+// B200_NORM_IMPL = tma (default: bulk-copy ring, csrc/norm_tma.cu) | warp | block: A/B switch for
+// tools/kernel_bench.py, read once.
+static int norm_impl() {
+  static int impl = -1;
+  if (impl < 0) {
+    const char* e = getenv("B200_NORM_IMPL");
+    impl = (e && e[0] == 'w') ? 1 : (e && e[0] == 'b') ? 2 : 0;
+  }
+  return impl;
+}
+
 static inline bool norm_shape_ok(int M, int H) {
   return M > 0 && H > 0 && (H % 8) == 0 && H <= kNormThreads * kNormMaxVec * 8;
 }
@@ -308,7 +327,9 @@ B200_API int b200_rmsnorm_fwd(const void* x, const void* residual, const void* w
                               void* h_out, float* rstd, int M, int H, float eps,
                               cudaStream_t stream) {
   if (!norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
-  if (rmsnorm_warp_ok(H)) {   // one warp per row (csrc/norm_warp.cu)
+  if (norm_impl() == 0 && rmsnorm_tma_ok(M, H))
+    return rmsnorm_fwd_tma(x, residual, w, y, h_out, rstd, M, H, eps, stream);
+  if (norm_impl() != 2 && rmsnorm_warp_ok(H)) {   // one warp per row (csrc/norm_warp.cu)
     rmsnorm_fwd_warp(x, residual, w, y, h_out, rstd, M, H, eps, stream);
     B200_CHECK_LAUNCH();
     return 0;
@@ -332,7 +353,9 @@ B200_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, cons
                               int accumulate, cudaStream_t stream) {
   if (!norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
   int grid = b200_norm_bwd_grid(M);
-  if (rmsnorm_warp_ok(H)) {
+  if (norm_impl() == 0 && rmsnorm_tma_ok(M, H))
+    return rmsnorm_bwd_tma(dy, x, w, rstd, dres, dx, dw, scratch, M, H, accumulate, stream);
+  if (norm_impl() != 2 && rmsnorm_warp_ok(H)) {
     rmsnorm_bwd_warp(dy, x, w, rstd, dres, dx, dw, scratch, grid, M, H, accumulate, stream);
     B200_CHECK_LAUNCH();
     return 0;

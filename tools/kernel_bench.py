@@ -169,32 +169,38 @@ def bench_attn_bwd():
 
 
 def bench_norm():
-    M, H = 4096, 4096
-    x = torch.randn(M, H, device="cuda").bfloat16()
-    w = torch.ones(H, device="cuda").bfloat16()
-    y = torch.empty_like(x)
-    rstd = torch.empty(M, device="cuda")
-    t_own = timeit(lambda: L.call("b200_rmsnorm_fwd", x.data_ptr(), None, w.data_ptr(), y.data_ptr(),
-                                  None, rstd.data_ptr(), M, H, 1e-5, L.stream_ptr()))
-
-    def eager():
-        xf = x.float()
-        return (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5)).type_as(x) * w
-    t_lib = timeit(eager)
-    by = 2.0 * M * H * 2
-    report(kernel="rmsnorm_fwd", M=M, H=H, ms_own=t_own, ms_eager=t_lib, gbs_own=by / t_own / 1e6,
-           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
-    dy = torch.randn_like(x)
-    dx = torch.empty_like(x)
-    dw = torch.zeros(H, device="cuda")
-    grid = L.lib().b200_norm_bwd_grid(M)
-    scratch = torch.empty(grid, H, device="cuda")
-    t_own = timeit(lambda: L.call("b200_rmsnorm_bwd", dy.data_ptr(), x.data_ptr(), w.data_ptr(),
-                                  rstd.data_ptr(), None, dx.data_ptr(), dw.data_ptr(),
-                                  scratch.data_ptr(), M, H, 0, L.stream_ptr()))
-    by = 3.0 * M * H * 2
-    report(kernel="rmsnorm_bwd", M=M, H=H, ms_own=t_own, gbs_own=by / t_own / 1e6,
-           frac_of_measured_hbm=by / t_own / 1e6 / PEAKS["hbm_gbs"])
+    """RMSNorm forward / backward, with and without the fused residual add (B200_NORM_IMPL=warp|block
+    in the environment selects the older register-resident kernels for an A/B)."""
+    impl = os.environ.get("B200_NORM_IMPL", "tma")
+    for M, H in ((4096, 4096), (2048, 4096), (4096, 5120), (2048, 8192)):
+        x = torch.randn(M, H, device="cuda").bfloat16()
+        res = torch.randn(M, H, device="cuda").bfloat16()
+        w = torch.ones(H, device="cuda").bfloat16()
+        y, h = torch.empty_like(x), torch.empty_like(x)
+        rstd = torch.empty(M, device="cuda")
+        dy = torch.randn_like(x)
+        dx = torch.empty_like(x)
+        dw = torch.zeros(H, device="cuda")
+        scratch = torch.empty(L.lib().b200_norm_bwd_grid(M), H, device="cuda")
+        for use_res in (False, True):
+            t = timeit(lambda: L.call("b200_rmsnorm_fwd", x.data_ptr(), L.ptr(res if use_res else None),
+                                      w.data_ptr(), y.data_ptr(), L.ptr(h if use_res else None),
+                                      rstd.data_ptr(), M, H, 1e-5, L.stream_ptr()))
+            by = (4.0 if use_res else 2.0) * M * H * 2
+            rec = dict(kernel="rmsnorm_fwd", impl=impl, residual=use_res, M=M, H=H, ms_own=t,
+                       gbs_own=by / t / 1e6, frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"])
+            if not use_res and (M, H) == (4096, 4096):
+                def eager():
+                    xf = x.float()
+                    return (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5)).type_as(x) * w
+                rec["ms_eager"] = timeit(eager)
+            report(**rec)
+            t = timeit(lambda: L.call("b200_rmsnorm_bwd", dy.data_ptr(), x.data_ptr(), w.data_ptr(),
+                                      rstd.data_ptr(), L.ptr(res if use_res else None), dx.data_ptr(),
+                                      dw.data_ptr(), scratch.data_ptr(), M, H, 0, L.stream_ptr()))
+            by = (4.0 if use_res else 3.0) * M * H * 2
+            report(kernel="rmsnorm_bwd(+dw)", impl=impl, dres=use_res, M=M, H=H, ms_own=t,
+                   gbs_own=by / t / 1e6, frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"])
 
 
 def bench_elementwise():

@@ -4,8 +4,13 @@
 //   mode AG  (all-gather -> GEMM): ColumnParallelLinear forward under sequence parallelism and
 //     the dgrad of RowParallelLinear (megatron/core/tensor_parallel/layers.py:225-243 and
 //     mappings.py:244-246 + the matmul behind them).  C[M, N] = gather_rows(X)[M, K] * B^T.
-//     Every CTA donates one warp that PULLS the other ranks' row chunks out of their staging
-//     buffers (16-byte peer loads over NVLink) into the local gathered matrix, 128-row block
+//     Every CTA donates two warps. They first copy the rank's own rows into its staging buffer
+//     (where the peers pull them from; guarded by the peers' "consumed" flags of two calls ago)
+//     and into their place in the gathered matrix, the last warp to finish raises the peers'
+//     shard_ready flag; the own-chunk tiles meanwhile read the caller's tensor directly through
+//     a second tensor map, so no separate staging kernel runs before the GEMM. Then the same warps
+//     PULL the other ranks' row chunks out of their staging buffers (16-byte peer loads over
+//     NVLink) into the local gathered matrix, 128-row block
 //     by 128-row block; a counter per block is bumped when a warp's share has landed. The
 //     TMA producers walk the output tiles starting with the rank's own chunk and only wait
 //     on a block's counter right before its first A tile is loaded, so the transfer of chunk
@@ -13,12 +18,18 @@
 //     caller keeps for the weight gradient (no second gather in backward).
 //   mode RS  (GEMM -> reduce-scatter): RowParallelLinear forward and the dgrad of
 //     ColumnParallelLinear (layers.py:691-692, :285-296).  out[M/tp, N] = sum_r (A_r B_r^T)[chunk].
-//     The epilogue converts each accumulator tile to bf16 and STORES it straight into the
-//     owning rank's slot for this source (peer stores), tiles owned by other ranks first;
-//     one warp-level release-add per tile quarter tells the owner. When a CTA has run out of
-//     tiles its epilogue warps reduce 8-row strips of the rank's own chunk (fp32 sum of the tp
-//     bf16 partials in rank order, so every rank computes the same bits) as soon as the
-//     strip's counters show all tp contributions.
+//     Tiles whose rows another rank owns come first: the epilogue converts the accumulators to
+//     bf16 and STORES the tile straight into the owner's slot for this source (TMA stores over
+//     NVLink), then bumps the owner's arrival counter of that tile (release at system scope).
+//     The rank's own tiles come last: by then the peers' partial tiles have long arrived, the
+//     epilogue waits on the tile's counter, adds the tp-1 partials to the fp32 accumulators on
+//     their way out of tensor memory and TMA-stores the FINAL tile -- the reduction is the
+//     epilogue of the tiles that would have produced the last partial anyway; no partial of the
+//     own chunk is ever written, no separate reduction pass reads the slots back.
+//   mode AR  (GEMM -> all-reduce): RowParallelLinear forward and ColumnParallelLinear dgrad WITHOUT
+//     sequence parallelism (layers.py:694, :278-283). Same as RS, but the owner stores each final
+//     tile into the output buffer of EVERY rank (peer TMA stores) and counts it there; the kernel
+//     ends once all tiles owned by other ranks have arrived.
 //
 // Protocol state lives in the symmetric workspace (csrc/comm.cu): monotonic u32 counters
 // compared with wrap-around arithmetic, one epoch per call. Waits on other GPUs are bounded:
@@ -41,7 +52,7 @@ constexpr int kOutBoxBytes = kBM * 128;                       // [128 rows x 64 
 constexpr int kOutOffset = kStages * kStageBytes;             // 4 boxes = the CTA's 128 x 256 tile
 constexpr int kBarOffset = kOutOffset + 4 * kOutBoxBytes, kSmemTotal = kBarOffset + 256 + 1024;
 constexpr int kMaxTP = 8;
-constexpr int kModeAG = 1, kModeRS = 2;
+constexpr int kModeAG = 1, kModeRS = 2, kModeAR = 3;
 
 struct CommArgs {
   // TMA store maps: [0] = C (AG mode) or, in RS mode, [o] = owner o's slot for source <me>
@@ -59,12 +70,22 @@ struct CommArgs {
   int max_blocks;
   unsigned* peer_consumed[kMaxTP];   // rank r's "rank <me> has pulled my shard" flag
   long long row_bytes;
-  // ---- reduce-scatter ----
-  unsigned* cnt_dst[kMaxTP];         // owner o's arrival counters [rows_per_chunk / 128]
+  const uint4* x_local;              // the caller's [rows_per_chunk, K] shard
+  uint4* stage_local;                // my staging shard of this call
+  const unsigned* consumed_local;    // [tp] epoch of the last pull each peer finished on stage_local's buffer pair
+  unsigned consumed_wait;            // peers must have finished this epoch's pull before stage_local is rewritten
+  int do_consumed_wait;
+  unsigned* signal_ready[kMaxTP];    // rank r's shard_ready[<me>] word
+  unsigned* stage_done;              // local monotonic counter of copier warps that finished staging
+  unsigned stage_done_target;
+  // ---- reduce-scatter / all-reduce ----
+  unsigned* cnt_dst[kMaxTP];         // owner o's arrival counters [rows_per_chunk / 128][tiles_n]
   const __nv_bfloat16* my_parts;     // my slots [tp][rows_per_chunk][N]
-  const unsigned* my_cnt;
-  unsigned rs_target;                // arrivals per row block in this call (counters start at 0)
-  __nv_bfloat16* out;                // [rows_per_chunk, N]
+  const unsigned* my_cnt;            // counters start at 0; a tile is complete at tp - 1
+  alignas(64) CUtensorMap final_map[kMaxTP];   // RS: [rank] = out [rows_per_chunk, N]; AR: [r] = rank r's out [M, N]
+  unsigned* ar_cnt_dst[kMaxTP];      // AR: rank r's "final tiles delivered" counter
+  const unsigned* my_ar_cnt;
+  unsigned ar_target;                // AR: final tiles (128 x 256) other ranks deliver to me
 };
 
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
@@ -126,6 +147,51 @@ __device__ __forceinline__ void spin_until(const unsigned* p, unsigned target, u
   }
 }
 
+// All-gather mode, warps 2..7 of every CTA at kernel start (the epilogue warps have nothing to do
+// until the first tile's MMAs are through): copy the rank's own rows into its staging buffer, where
+// the peers pull them from, and into their place in the gathered matrix. The buffer's previous
+// content (two calls ago) must have been pulled by every peer first; the last warp to finish raises
+// the peers' shard_ready flags.
+constexpr int kStageWarps = 6;
+__device__ __forceinline__ void stage_own_rows(const CommArgs& ca, int w, int lane) {
+  const int nw = kStageWarps * gridDim.x;
+  if (ca.do_consumed_wait) {
+    if (lane < ca.tp && lane != ca.rank)
+      spin_until<true>(&ca.consumed_local[lane], ca.consumed_wait, 5u, lane, ca.epoch, ca.mode, ca.rank);
+    __syncwarp();
+  }
+  const long long nseg = (long long)ca.rows_per_chunk * (ca.row_bytes / 512);   // 512 B = one warp access
+  const uint4* xs = ca.x_local + lane;
+  uint4* sd = ca.stage_local + lane;
+  uint4* gd = ca.gathered + (long long)ca.rank * ca.rows_per_chunk * (ca.row_bytes / 16) + lane;
+  constexpr int U0 = 8;
+  for (long long sg = w; sg < nseg; sg += (long long)nw * U0) {
+    uint4 v[U0];
+#pragma unroll
+    for (int u = 0; u < U0; ++u) {
+      const long long g = sg + (long long)u * nw;
+      if (g < nseg) v[u] = xs[g * 32];
+    }
+#pragma unroll
+    for (int u = 0; u < U0; ++u) {
+      const long long g = sg + (long long)u * nw;
+      if (g < nseg) {
+        sd[g * 32] = v[u];
+        gd[g * 32] = v[u];
+      }
+    }
+  }
+  __threadfence_system();
+  __syncwarp();
+  if (lane == 0) {
+    const unsigned old = atomicAdd(ca.stage_done, 1u);
+    if (old + 1u == ca.stage_done_target) {
+      __threadfence_system();
+      for (int q = 1; q < ca.tp; ++q) st_release_sys(ca.signal_ready[(ca.rank + q) % ca.tp], ca.epoch);
+    }
+  }
+}
+
 __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int& tm, int& tn) {
   const int group = kGroupM * tiles_n;
   const int gid = tile / group;
@@ -138,9 +204,9 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
 
 template <bool kBMN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 __nv_bfloat16* __restrict__ Cout, int M, int N, int K, long long ldc,
-                 const __grid_constant__ CommArgs ca) {
+gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmAloc,
+                 const __grid_constant__ CUtensorMap tmB, __nv_bfloat16* __restrict__ Cout, int M, int N,
+                 int K, long long ldc, const __grid_constant__ CommArgs ca) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
@@ -165,6 +231,7 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmAloc);
     tma_prefetch_desc(&tmB);
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
@@ -194,7 +261,11 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tm = (tm + tm_rot) % tiles_m;
         const int m0 = tm * 2 * kBM + static_cast<int>(crank) * kBM;
         const int n0 = tn * kBN + static_cast<int>(crank) * kHalfN;
-        if (ca.mode == kModeAG && m0 < M && m0 / ca.rows_per_chunk != ca.rank) {
+        // own rows (all-gather mode) are read from the caller's shard, not from the gathered matrix
+        const bool local_a = ca.mode == kModeAG && m0 / ca.rows_per_chunk == ca.rank;
+        const CUtensorMap* ma = local_a ? &tmAloc : &tmA;
+        const int ma_row = local_a ? m0 - ca.rank * ca.rows_per_chunk : m0;
+        if (ca.mode == kModeAG && m0 < M && !local_a) {
           // rows pulled from another GPU by the copier warps: wait for this 128-row block
           spin_until<false>(&ca.row_ready[m0 / kBM], ready_target, 1u, m0 / kBM, ca.epoch, ca.mode, ca.rank);
           fence_proxy_async_global();
@@ -204,7 +275,7 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           uint8_t* sa = smem + stage * kStageBytes;
           uint8_t* sb = sa + kABytes;
           if (crank == 0) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
-          tma_load_2d_pair(sa, &tmA, &full_bar[stage], kb * kBK, m0);
+          tma_load_2d_pair(sa, ma, &full_bar[stage], kb * kBK, ma_row);
           if (!kBMN) {
             tma_load_2d_pair(sb, &tmB, &full_bar[stage], kb * kBK, n0);
           } else {
@@ -267,6 +338,7 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       const long long segs_per_block = (long long)kBM * (ca.row_bytes / 512);  // 512 B = one warp access
       const int nrb = ca.rows_per_chunk / kBM;
+      stage_own_rows(ca, blockIdx.x * kStageWarps + (warp - 2), lane);
       for (int step = 1; step < ca.tp; ++step) {
         const int src = (ca.rank + step) % ca.tp;
         if (lane == 0) spin_until<true>(&ca.shard_ready[src], ca.epoch, 2u, src, ca.epoch, ca.mode, ca.rank);
@@ -311,22 +383,64 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const uint32_t leader_empty0 = mapa_u32(smem_u32(&tmem_empty[0]), 0);
     uint8_t* stage_out = smem + kOutOffset;
     const bool issuer = (ew == 0 && lane == 0);
+    const bool reduce_mode = ca.mode != kModeAG;
+    if (!reduce_mode) stage_own_rows(ca, blockIdx.x * kStageWarps + (warp - 2), lane);
+    const size_t slot = (size_t)ca.rows_per_chunk * N;
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int tm, tn;
       tile_coords(tile, tiles_m, tiles_n, tm, tn);
       tm = (tm + tm_rot) % tiles_m;
       const int row0 = tm * 2 * kBM + static_cast<int>(crank) * kBM;
       const int n0 = tn * kBN;
+      int owner = 0, drow = row0;
+      if (reduce_mode) {
+        owner = row0 / ca.rows_per_chunk;
+        drow = row0 - owner * ca.rows_per_chunk;
+      }
+      const bool own = reduce_mode && owner == ca.rank;
+      const int cidx = (drow / kBM) * tiles_n + tn;
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
+      if (own) {
+        // every peer's partial of this 128 x 256 tile has landed in my slots
+        if (lane == 0)
+          spin_until<true>(&ca.my_cnt[cidx], (unsigned)(ca.tp - 1), 3u, cidx, ca.epoch, ca.mode, ca.rank);
+        __syncwarp();
+      }
       if (issuer) tma_store_wait_read<0>();          // the previous tile's boxes have been read
       asm volatile("bar.sync 1, 128;" ::: "memory");
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN;
+      const __nv_bfloat16* prow = ca.my_parts + (size_t)(drow + r) * N + n0;
 #pragma unroll 1
       for (int c = 0; c < kBN / 32; ++c) {
         uint32_t v[32];
         tmem_ld_32x32(taddr + c * 32, v);
-        tmem_ld_wait();
+        if (own) {
+          // fp32 sum of the peers' bf16 partials (rank order), added to the accumulators
+          float pacc[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) pacc[k] = 0.f;
+          for (int p = 0; p < ca.tp; ++p) {
+            if (p == ca.rank) continue;
+            const uint4* src = reinterpret_cast<const uint4*>(prow + (size_t)p * slot + c * 32);
+            uint4 q[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              q[j] = (n0 + c * 32 + j * 8 < N) ? __ldcv(src + j) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float f[8];
+              unpack8(q[j], f);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) pacc[j * 8 + k] += f[k];
+            }
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 32; ++k) v[k] = __float_as_uint(__uint_as_float(v[k]) + pacc[k]);
+        } else {
+          tmem_ld_wait();
+        }
         uint8_t* box = stage_out + (c >> 1) * kOutBoxBytes;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
@@ -344,21 +458,41 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (issuer && row0 < M) {
-        int owner = 0, drow = row0;
-        if (ca.mode == kModeRS) {
-          owner = row0 / ca.rows_per_chunk;
-          drow = row0 - owner * ca.rows_per_chunk;
-        }
-        const CUtensorMap* om = &ca.out_map[ca.mode == kModeRS ? owner : 0];
+        if (!reduce_mode) {
 #pragma unroll
-        for (int bx = 0; bx < 4; ++bx)
-          if (n0 + bx * 64 < N) tma_store_2d(om, stage_out + bx * kOutBoxBytes, n0 + bx * 64, drow);
-        tma_store_commit();
-        if (ca.mode == kModeRS) {
+          for (int bx = 0; bx < 4; ++bx)
+            if (n0 + bx * 64 < N) tma_store_2d(&ca.out_map[0], stage_out + bx * kOutBoxBytes, n0 + bx * 64, row0);
+          tma_store_commit();
+        } else if (!own) {
+          // partial tile -> the owner's slot for this source, then tell the owner
+#pragma unroll
+          for (int bx = 0; bx < 4; ++bx)
+            if (n0 + bx * 64 < N) tma_store_2d(&ca.out_map[owner], stage_out + bx * kOutBoxBytes, n0 + bx * 64, drow);
+          tma_store_commit();
           tma_store_wait<0>();              // the partial rows have been written ...
           fence_proxy_async_global();
           __threadfence_system();           // ... and are visible before the owner counts them
-          red_release_sys_add(ca.cnt_dst[owner] + drow / kBM, 1u);
+          red_release_sys_add(ca.cnt_dst[owner] + cidx, 1u);
+        } else if (ca.mode == kModeRS) {
+#pragma unroll
+          for (int bx = 0; bx < 4; ++bx)
+            if (n0 + bx * 64 < N)
+              tma_store_2d(&ca.final_map[ca.rank], stage_out + bx * kOutBoxBytes, n0 + bx * 64, drow);
+          tma_store_commit();
+        } else {
+          // all-reduce: the final tile goes to every rank's output (mine first)
+          for (int q = 0; q < ca.tp; ++q) {
+            const int dst = (ca.rank + q) % ca.tp;
+#pragma unroll
+            for (int bx = 0; bx < 4; ++bx)
+              if (n0 + bx * 64 < N)
+                tma_store_2d(&ca.final_map[dst], stage_out + bx * kOutBoxBytes, n0 + bx * 64, row0);
+          }
+          tma_store_commit();
+          tma_store_wait<0>();
+          fence_proxy_async_global();
+          __threadfence_system();
+          for (int q = 1; q < ca.tp; ++q) red_release_sys_add(ca.ar_cnt_dst[(ca.rank + q) % ca.tp], 1u);
         }
       }
       if (++as == 2) {
@@ -369,54 +503,9 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (issuer) tma_store_wait<0>();
   }
 
-  if (ca.mode == kModeRS) {
-    // ------------------------------ reduce own chunk --------------------------
-    // All 8 warps join once their role loop is over (lanes that had no role get here first
-    // and meet their warp's lane 0 at the __syncwarp below). A unit is an 8-row strip; the
-    // strip is summed as soon as its 128-row block has received every rank's tile pieces.
-    const unsigned target = ca.rs_target;
-    const int units = ca.rows_per_chunk / 8;
-    const int vec_per_row = N / 8;
-    const int vecs = 8 * vec_per_row;
-    const size_t slot = (size_t)ca.rows_per_chunk * N;
-    for (int unit = blockIdx.x; unit < units; unit += gridDim.x) {
-      const int r0 = unit * 8;
-      if (lane == 0) spin_until<true>(&ca.my_cnt[r0 / kBM], target, 3u, r0 / kBM, ca.epoch, ca.mode, ca.rank);
-      __syncwarp();
-      const size_t base = (size_t)r0 * N;
-      constexpr int V = 4;
-      for (int idx = threadIdx.x; idx < vecs; idx += kThreads * V) {
-        float acc[V][8];
-#pragma unroll
-        for (int u = 0; u < V; ++u)
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[u][j] = 0.f;
-        for (int sidx = 0; sidx < ca.tp; ++sidx) {
-          uint4 v[V];
-#pragma unroll
-          for (int u = 0; u < V; ++u) {
-            const int id = idx + u * kThreads;
-            if (id < vecs)
-              v[u] = __ldcv(reinterpret_cast<const uint4*>(ca.my_parts + sidx * slot + base + (size_t)id * 8));
-          }
-#pragma unroll
-          for (int u = 0; u < V; ++u) {
-            float f[8];
-            unpack8(*reinterpret_cast<const bf16x8*>(&v[u]), f);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[u][j] += f[j];
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < V; ++u) {
-          const int id = idx + u * kThreads;
-          if (id < vecs) {
-            const bf16x8 o = pack8(acc[u]);
-            *reinterpret_cast<uint4*>(ca.out + base + (size_t)id * 8) = *reinterpret_cast<const uint4*>(&o);
-          }
-        }
-      }
-    }
+  if (ca.mode == kModeAR && threadIdx.x == 0) {
+    // the output is complete on this rank once every tile owned by another rank has arrived
+    spin_until<true>(ca.my_ar_cnt, ca.ar_target, 4u, 0u, ca.epoch, ca.mode, ca.rank);
   }
 
   tc_fence_before();
@@ -433,8 +522,8 @@ static int make_out_map(CUtensorMap* map, void* base, long long rows, long long 
 }
 
 template <bool kBMN>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, int K, long long ldc,
-           const CommArgs& ca, cudaStream_t stream) {
+int launch(const CUtensorMap& ta, const CUtensorMap& taloc, const CUtensorMap& tb, void* C, int M, int N, int K,
+           long long ldc, const CommArgs& ca, cudaStream_t stream) {
   auto kern = gemm_comm_kernel<kBMN>;
   static bool configured = false;
   if (!configured) {
@@ -443,7 +532,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, 
     configured = true;
   }
   // every CTA takes part in the collective, so the grid is always the full machine
-  kern<<<kNumSMs, kThreads, kSmemTotal, stream>>>(ta, tb, (__nv_bfloat16*)C, M, N, K, ldc, ca);
+  kern<<<kNumSMs, kThreads, kSmemTotal, stream>>>(ta, taloc, tb, (__nv_bfloat16*)C, M, N, K, ldc, ca);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -456,19 +545,26 @@ using b200::fc::CommArgs;
 
 // Workspace layout (all pointers are device addresses valid on THIS GPU; peer_* entries point
 // into the other ranks' workspaces through the IPC mappings of csrc/comm.cu):
-//   flags (u32): row_ready[2][max_blocks] | shard_ready[8] | chunk_done[2][8] | consumed[8] | rs_cnt[2][max_blocks]
+//   flags (u32): row_ready[2][max_blocks] | shard_ready[8] | chunk_done[2][8] | consumed[8] |
+//                (legacy rs_cnt[2][max_blocks]) | tile_cnt[2][max_blocks * max_tn] | ar_cnt[2] (+ pad)
 struct B200CommDesc {
   int tp, rank;
   void* peer_stage[8];        // rank r's staging shard
   unsigned* peer_flags[8];    // rank r's flag block
   int max_blocks;
+  int max_tn;                 // widest reduce-scattered output in 256-column tiles
 };
 
 static inline unsigned* f_row_ready(unsigned* f, int mb, int set) { return f + set * mb; }
 static inline unsigned* f_shard_ready(unsigned* f, int mb) { return f + 2 * mb; }
 static inline unsigned* f_chunk_done(unsigned* f, int mb, int set) { return f + 2 * mb + 8 + set * 8; }
 static inline unsigned* f_consumed(unsigned* f, int mb) { return f + 2 * mb + 24; }
-static inline unsigned* f_rs_cnt(unsigned* f, int mb, int set) { return f + 2 * mb + 32 + set * mb; }
+static inline unsigned* f_tile_cnt(unsigned* f, int mb, int mtn, int set) {
+  return f + 4 * mb + 32 + set * mb * mtn;
+}
+static inline unsigned* f_ar_cnt(unsigned* f, int mb, int mtn, int set) {
+  return f + 4 * mb + 32 + 2 * mb * mtn + set;
+}
 
 // Copies the 8-word record of the first timed-out wait on this GPU (all zero = none) and clears it.
 B200_API int b200_comm_debug_read(unsigned* out8) {
@@ -478,22 +574,29 @@ B200_API int b200_comm_debug_read(unsigned* out8) {
   return (int)cudaMemcpyToSymbol(fc::g_comm_debug, z, sizeof(z));
 }
 
-B200_API int b200_comm_flag_words(int max_blocks) { return 4 * max_blocks + 32; }
+B200_API int b200_comm_flag_words(int max_blocks, int max_tn) {
+  return 4 * max_blocks + 32 + 2 * max_blocks * max_tn + 16;
+}
 // word offsets of the flag blocks the host side signals / waits on
 B200_API int b200_comm_shard_ready_word(int max_blocks) { return 2 * max_blocks; }
 B200_API int b200_comm_consumed_word(int max_blocks) { return 2 * max_blocks + 24; }
 
-// C[M, N] = gathered[M, K] * B^T where gathered rows [r*M/tp, (r+1)*M/tp) come from rank r's
-// staging shard (the caller has already placed its own chunk into `gathered`). epoch: 1, 2, ...
-// per call on this workspace, identical on all ranks.
-B200_API int b200_gemm_allgather(const B200CommDesc* d, void* gathered, const void* B, void* C, int M,
-                                 int N, int K, int b_mn_major, long long ldb, long long ldc,
-                                 unsigned epoch, cudaStream_t stream) {
-  if (!d || d->tp < 2 || d->tp > 8 || M % d->tp) return B200_ERR_BAD_ARG;
+// C[M, N] = gathered[M, K] * B^T where gathered rows [r*M/tp, (r+1)*M/tp) are rank r's x_shard
+// [M/tp, K]: the kernel stages the own shard for the peers, fills `gathered` (own rows copied, the
+// others pulled over NVLink) and multiplies, own rows first. epoch: 1, 2, ... per call on this
+// workspace, identical on all ranks; `d` must be the descriptor of staging buffer (epoch & 1);
+// stage_done: a local u32 counter used only by this entry point (zero at workspace creation).
+B200_API int b200_gemm_allgather(const B200CommDesc* d, const void* x_shard, void* gathered, const void* B,
+                                 void* C, int M, int N, int K, int b_mn_major, long long ldb,
+                                 long long ldc, unsigned epoch, unsigned* stage_done,
+                                 cudaStream_t stream) {
+  if (!d || d->tp < 2 || d->tp > 8 || M % d->tp || !x_shard || !stage_done) return B200_ERR_BAD_ARG;
   const int rpc = M / d->tp;
   if (rpc % 256 || (K * 2) % 512 || M / 128 > d->max_blocks) return B200_ERR_UNSUPPORTED;
-  CUtensorMap ta, tb;
+  CUtensorMap ta, taloc, tb;
   int rc = make_tmap_2d(&ta, gathered, M, K, K, fc::kBM);
+  if (rc) return rc;
+  rc = make_tmap_2d(&taloc, x_shard, rpc, K, K, fc::kBM);
   if (rc) return rc;
   rc = b_mn_major ? make_tmap_2d(&tb, B, K, N, ldb, fc::kBK) : make_tmap_2d(&tb, B, N, K, ldb, fc::kHalfN);
   if (rc) return rc;
@@ -507,6 +610,7 @@ B200_API int b200_gemm_allgather(const B200CommDesc* d, void* gathered, const vo
   for (int r = 0; r < d->tp; ++r) {
     ca.peer_src[r] = (const uint4*)d->peer_stage[r];
     ca.peer_consumed[r] = f_consumed(d->peer_flags[r], d->max_blocks) + d->rank;
+    ca.signal_ready[r] = f_shard_ready(d->peer_flags[r], d->max_blocks) + d->rank;
   }
   ca.gathered = (uint4*)gathered;
   const int set = (int)(epoch & 1u);   // per-call counters alternate; each call clears the other set
@@ -517,50 +621,86 @@ B200_API int b200_gemm_allgather(const B200CommDesc* d, void* gathered, const vo
   ca.chunk_done_next = f_chunk_done(mine, d->max_blocks, set ^ 1);
   ca.max_blocks = d->max_blocks;
   ca.row_bytes = (long long)K * 2;
+  ca.x_local = (const uint4*)x_shard;
+  ca.stage_local = (uint4*)d->peer_stage[d->rank];
+  ca.consumed_local = f_consumed(mine, d->max_blocks);
+  ca.consumed_wait = epoch - 2u;       // the previous user of this staging buffer
+  ca.do_consumed_wait = epoch > 2u;
+  ca.stage_done = stage_done;
+  ca.stage_done_target = epoch * (unsigned)(fc::kStageWarps * kNumSMs);   // warps 2..7 of every CTA, every call
   rc = fc::make_out_map(&ca.out_map[0], C, M, N, ldc);
   if (rc) return rc;
-  return b_mn_major ? fc::launch<true>(ta, tb, C, M, N, K, ldc, ca, stream)
-                    : fc::launch<false>(ta, tb, C, M, N, K, ldc, ca, stream);
+  return b_mn_major ? fc::launch<true>(ta, taloc, tb, C, M, N, K, ldc, ca, stream)
+                    : fc::launch<false>(ta, taloc, tb, C, M, N, K, ldc, ca, stream);
 }
 
-// Arrivals a 128-row block of the owner's counters receives in one reduce-scatter call.
-B200_API int b200_gemm_rs_arrivals(int N, int tp) { return ((N + fc::kBN - 1) / fc::kBN) * tp; }
-
-// out[M/tp, N] = rows chunk <rank> of sum over ranks of A_r[M, K] * B_r^T. The workspace has two
-// sets of partial-sum slots and arrival counters; callers alternate `set` call by call, which is
-// enough to keep a fast rank from touching state a slow rank still reads (a rank can finish call
-// e+1 only after every peer has finished call e). peer_parts[r] = rank r's slots of that set;
-// rs_target = b200_gemm_rs_arrivals(N, tp). The owner zeroes the set's counters after its kernel.
-B200_API int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int set,
-                                      const void* A, const void* B, void* out, int M, int N, int K,
-                                      int b_mn_major, long long lda, long long ldb,
-                                      unsigned rs_target, cudaStream_t stream) {
+// Shared set-up of the reduce-scatter / all-reduce GEMMs. peer_parts[r] = rank r's partial-sum
+// slots of `set`; the workspace has two sets of slots and counters and callers alternate `set`
+// call by call, which is enough to keep a fast rank from touching state a slow rank still reads
+// (a rank can finish call e+1 only after every peer has delivered its partials of call e+1, i.e.
+// after every peer has finished call e). The owner zeroes the set's counters after its kernel.
+static int reduce_gemm(const B200CommDesc* d, void* const* peer_parts, void* const* peer_out, int set,
+                       const void* A, const void* B, void* out, int M, int N, int K, int b_mn_major,
+                       long long lda, long long ldb, cudaStream_t stream) {
   if (!d || d->tp < 2 || d->tp > 8 || M % d->tp || set < 0 || set > 1) return B200_ERR_BAD_ARG;
   const int rpc = M / d->tp;
-  if (rpc % 256 || N % 8 || M / 128 > d->max_blocks || (lda % 8) || (ldb % 8)) return B200_ERR_UNSUPPORTED;
+  const int tiles_n = (N + fc::kBN - 1) / fc::kBN;
+  if (rpc % 256 || N % 8 || M / 128 > d->max_blocks || tiles_n > d->max_tn || (lda % 8) || (ldb % 8))
+    return B200_ERR_UNSUPPORTED;
   CUtensorMap ta, tb;
   int rc = make_tmap_2d(&ta, A, M, K, lda, fc::kBM);
   if (rc) return rc;
   rc = b_mn_major ? make_tmap_2d(&tb, B, K, N, ldb, fc::kBK) : make_tmap_2d(&tb, B, N, K, ldb, fc::kHalfN);
   if (rc) return rc;
   CommArgs ca = {};
-  ca.mode = fc::kModeRS;
+  ca.mode = peer_out ? fc::kModeAR : fc::kModeRS;
   ca.tp = d->tp;
   ca.rank = d->rank;
   ca.rows_per_chunk = rpc;
-  ca.rs_target = rs_target;
   const size_t slot = (size_t)rpc * N;
   for (int o = 0; o < d->tp; ++o) {
     rc = fc::make_out_map(&ca.out_map[o], (__nv_bfloat16*)peer_parts[o] + slot * d->rank, rpc, N, N);
     if (rc) return rc;
-    ca.cnt_dst[o] = f_rs_cnt(d->peer_flags[o], d->max_blocks, set);
+    ca.cnt_dst[o] = f_tile_cnt(d->peer_flags[o], d->max_blocks, d->max_tn, set);
+    if (peer_out) {
+      rc = fc::make_out_map(&ca.final_map[o], peer_out[o], M, N, N);
+      if (rc) return rc;
+      ca.ar_cnt_dst[o] = f_ar_cnt(d->peer_flags[o], d->max_blocks, d->max_tn, set);
+    }
   }
   ca.my_parts = (const __nv_bfloat16*)peer_parts[d->rank];
-  ca.my_cnt = f_rs_cnt(d->peer_flags[d->rank], d->max_blocks, set);
-  ca.out = (__nv_bfloat16*)out;
-  rc = b_mn_major ? fc::launch<true>(ta, tb, nullptr, M, N, K, N, ca, stream)
-                  : fc::launch<false>(ta, tb, nullptr, M, N, K, N, ca, stream);
+  unsigned* my_cnt = f_tile_cnt(d->peer_flags[d->rank], d->max_blocks, d->max_tn, set);
+  unsigned* my_ar = f_ar_cnt(d->peer_flags[d->rank], d->max_blocks, d->max_tn, set);
+  ca.my_cnt = my_cnt;
+  ca.my_ar_cnt = my_ar;
+  ca.ar_target = (unsigned)(((M - rpc) / fc::kBM) * tiles_n);
+  if (!peer_out) {
+    rc = fc::make_out_map(&ca.final_map[d->rank], out, rpc, N, N);
+    if (rc) return rc;
+  }
+  rc = b_mn_major ? fc::launch<true>(ta, ta, tb, nullptr, M, N, K, N, ca, stream)
+                  : fc::launch<false>(ta, ta, tb, nullptr, M, N, K, N, ca, stream);
   if (rc) return rc;
   // peers touch this set again two calls from now at the earliest (see above)
-  return (int)cudaMemsetAsync(const_cast<unsigned*>(ca.my_cnt), 0, sizeof(unsigned) * (rpc / 128), stream);
+  cudaError_t e = cudaMemsetAsync(my_cnt, 0, sizeof(unsigned) * (rpc / fc::kBM) * tiles_n, stream);
+  if (e == cudaSuccess && peer_out) e = cudaMemsetAsync(my_ar, 0, sizeof(unsigned), stream);
+  return (int)e;
+}
+
+// out[M/tp, N] = rows chunk <rank> of sum over ranks of A_r[M, K] * B_r^T.
+B200_API int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int set,
+                                      const void* A, const void* B, void* out, int M, int N, int K,
+                                      int b_mn_major, long long lda, long long ldb,
+                                      cudaStream_t stream) {
+  return reduce_gemm(d, peer_parts, nullptr, set, A, B, out, M, N, K, b_mn_major, lda, ldb, stream);
+}
+
+// Every rank's peer_out[r] (rank r's [M, N] output buffer of `set`, peer-mapped) receives
+// sum over ranks of A_r[M, K] * B_r^T: the reduce-scatter above with the owner of a row chunk
+// storing its final tiles into all tp outputs.
+B200_API int b200_gemm_allreduce(const B200CommDesc* d, void* const* peer_parts, void* const* peer_out,
+                                 int set, const void* A, const void* B, int M, int N, int K,
+                                 int b_mn_major, long long lda, long long ldb, cudaStream_t stream) {
+  if (!peer_out) return B200_ERR_BAD_ARG;
+  return reduce_gemm(d, peer_parts, peer_out, set, A, B, nullptr, M, N, K, b_mn_major, lda, ldb, stream);
 }

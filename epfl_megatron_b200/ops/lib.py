@@ -64,7 +64,7 @@ _SIGNATURES = {
     "b200_symm_signal": ([vp, i32, C.c_uint, vp], i32),
     "b200_symm_wait": ([vp, i32, i32, C.c_uint, vp], i32),
     "b200_copy2": ([vp, vp, vp, i64, vp], i32),
-    "b200_comm_flag_words": ([i32], i32),
+    "b200_comm_flag_words": ([i32, i32], i32),
     "b200_comm_shard_ready_word": ([i32], i32),
     "b200_comm_consumed_word": ([i32], i32),
     "b200_stage_shard": ([vp, vp, vp, i64, vp, i32, i32, C.c_uint, i32, vp, C.c_uint, vp, i32, C.c_uint, vp], i32),
@@ -74,9 +74,9 @@ _SIGNATURES = {
     "b200_dp_wait": ([vp, i32, i32, C.c_uint, C.c_uint, vp], i32),
     "b200_dp_debug_read": ([vp], i32),
     "b200_copy_async": ([vp, vp, i64, vp], i32),
-    "b200_gemm_rs_arrivals": ([i32, i32], i32),
-    "b200_gemm_allgather": ([vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp], i32),
-    "b200_gemm_reduce_scatter": ([vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp], i32),
+    "b200_gemm_allgather": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp, vp], i32),
+    "b200_gemm_reduce_scatter": ([vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i64, i64, vp], i32),
+    "b200_gemm_allreduce": ([vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, i64, i64, vp], i32),
 }
 
 _OPTIONAL = set()

@@ -3,9 +3,10 @@
 Every rank of the group owns one region (csrc/comm.cu: cudaMalloc + CUDA IPC export), laid out as
 
     flags | 2 staging shards [rows_per_chunk, K] | 2 sets of partial-sum slots [tp][rows_per_chunk][N]
+          | (only when all-reduce GEMMs are used: 2 output buffers [rows, N])
 
-and maps the regions of its peers. ``allgather_gemm`` and ``gemm_reduce_scatter`` launch ONE
-kernel each (csrc/gemm_comm_tcgen05.cu) that moves activation rows over NVLink from inside the
+and maps the regions of its peers. ``allgather_gemm``, ``gemm_reduce_scatter`` and ``gemm_allreduce``
+launch ONE kernel each (csrc/gemm_comm_tcgen05.cu) that moves activation rows over NVLink from inside the
 GEMM: they replace the all-gather + matmul of ColumnParallelLinear and the matmul +
 reduce-scatter of RowParallelLinear under sequence parallelism
 (megatron/core/tensor_parallel/layers.py:225-243, :691-692; mappings.py:89-124).
@@ -27,7 +28,7 @@ from ..ops import lib as L
 
 class _Desc(C.Structure):
     _fields_ = [("tp", C.c_int), ("rank", C.c_int), ("peer_stage", C.c_void_p * 8),
-                ("peer_flags", C.c_void_p * 8), ("max_blocks", C.c_int)]
+                ("peer_flags", C.c_void_p * 8), ("max_blocks", C.c_int), ("max_tn", C.c_int)]
 
 
 def _wrap(ptr: int, nbytes: int, device) -> torch.Tensor:
@@ -42,7 +43,7 @@ class TPWorkspace:
     """max_rows: largest M (= s*b) of a gathered activation; max_k / max_n: widest gathered input /
     reduce-scattered output in elements."""
 
-    def __init__(self, group, max_rows: int, max_k: int, max_n: int):
+    def __init__(self, group, max_rows: int, max_k: int, max_n: int, allreduce: bool = False):
         self.group = group
         self.tp = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
@@ -52,14 +53,17 @@ class TPWorkspace:
         self.max_rows, self.max_k, self.max_n = max_rows, max_k, max_n
         self.max_blocks = (max_rows + 127) // 128
         rpc = max_rows // self.tp
-        words = lib.b200_comm_flag_words(self.max_blocks)
+        self.max_tn = (max_n + 255) // 256
+        self.allreduce = allreduce
+        words = lib.b200_comm_flag_words(self.max_blocks, self.max_tn)
         self.w_ready = lib.b200_comm_shard_ready_word(self.max_blocks)
         self.w_consumed = lib.b200_comm_consumed_word(self.max_blocks)
         self.w_stage_done = words            # one extra word: completion counter of the staging kernel
         self.flag_bytes = ((words + 1) * 4 + 4095) // 4096 * 4096
         self.stage_bytes = (rpc * max_k * 2 + 4095) // 4096 * 4096
         self.parts_bytes = (self.tp * rpc * max_n * 2 + 4095) // 4096 * 4096
-        self.nbytes = self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes
+        self.out_bytes = (max_rows * max_n * 2 + 4095) // 4096 * 4096 if allreduce else 0
+        self.nbytes = self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes + 2 * self.out_bytes
         base = C.c_void_p()
         L.call("b200_symm_alloc", self.nbytes, C.byref(base), launches=0)
         self.base = base.value
@@ -98,12 +102,15 @@ class TPWorkspace:
     def _parts(self, r, s):
         return self.peer_base[r] + self.flag_bytes + 2 * self.stage_bytes + s * self.parts_bytes
 
+    def _out(self, r, s):
+        return self.peer_base[r] + self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes + s * self.out_bytes
+
     def _flag(self, r, word):
         return self.peer_base[r] + 4 * word
 
     def _make_desc(self, stage):
         d = _Desc()
-        d.tp, d.rank, d.max_blocks = self.tp, self.rank, self.max_blocks
+        d.tp, d.rank, d.max_blocks, d.max_tn = self.tp, self.rank, self.max_blocks, self.max_tn
         for r in range(self.tp):
             d.peer_stage[r] = self._stage(r, stage)
             d.peer_flags[r] = self.peer_base[r]
@@ -123,20 +130,13 @@ class TPWorkspace:
         stage = e % 2
         st = L.stream_ptr()
         gathered = torch.empty(M, K, device=self.device, dtype=torch.bfloat16)
-        own = gathered[self.rank * rpc:(self.rank + 1) * rpc]
-        addrs = (C.c_void_p * 8)()
-        n = 0
-        for r in range(self.tp):
-            if r != self.rank:
-                addrs[n] = self._flag(r, self.w_ready + self.rank)      # rank r's shard_ready[me]
-                n += 1
-        # wait (peers pulled this staging shard's previous content, epoch e-2) + copy + signal
-        L.call("b200_stage_shard", x_shard.data_ptr(), self._stage(self.rank, stage), own.data_ptr(),
-               rpc * K * 2, self._flag(self.rank, self.w_consumed), self.tp, self.rank, (e - 2) & 0xFFFFFFFF,
-               int(e > 2), self._flag(self.rank, self.w_stage_done), e, addrs, n, e, st)
         out = torch.empty(M, N, device=self.device, dtype=torch.bfloat16)
-        L.call("b200_gemm_allgather", C.byref(self._descs[stage]), gathered.data_ptr(), weight.data_ptr(),
-               out.data_ptr(), M, N, K, int(b_mn_major), weight.stride(0), N, e, st)
+        # ONE launch: the kernel's copier warps stage the own rows for the peers (after the peers
+        # reported having pulled this staging buffer's previous content, epoch e-2), raise the
+        # peers' shard_ready flags and pull the other chunks while the own rows are multiplied
+        L.call("b200_gemm_allgather", C.byref(self._descs[stage]), x_shard.data_ptr(), gathered.data_ptr(),
+               weight.data_ptr(), out.data_ptr(), M, N, K, int(b_mn_major), weight.stride(0), N, e,
+               self._flag(self.rank, self.w_stage_done), st)
         if self.verify:
             ref = torch.empty_like(gathered)
             dist.all_gather_into_tensor(ref, x_shard, group=self.group)
@@ -159,14 +159,12 @@ class TPWorkspace:
         assert M <= self.max_rows and N <= self.max_n, (M, N, self.max_rows, self.max_n)
         self.rs_calls += 1
         s = self.rs_calls % 2
-        arrivals = L.lib().b200_gemm_rs_arrivals(N, self.tp)
         parts = (C.c_void_p * 8)()
         for r in range(self.tp):
             parts[r] = self._parts(r, s)
         out = torch.empty(rpc, N, device=self.device, dtype=torch.bfloat16)
         L.call("b200_gemm_reduce_scatter", C.byref(self._descs[0]), parts, s, a.data_ptr(), weight.data_ptr(),
-               out.data_ptr(), M, N, K, int(b_mn_major), a.stride(0), weight.stride(0),
-               arrivals, L.stream_ptr())
+               out.data_ptr(), M, N, K, int(b_mn_major), a.stride(0), weight.stride(0), L.stream_ptr())
         if self.poison:
             self._parts_view[s].fill_(-1)       # 0xFFFF = bf16 NaN; consumed slots of this call only
         if self.verify:
@@ -177,6 +175,33 @@ class TPWorkspace:
             if not err <= 3e-2 * max(want.abs().max().item(), 1.0):
                 raise RuntimeError(f"fused GEMM reduce-scatter (call {self.rs_calls}, rank {self.rank}): "
                                    f"max abs error {err}")
+        return out
+
+    # ---- GEMM -> all-reduce (tensor parallelism without sequence parallelism) ---------------
+    def gemm_allreduce(self, a: torch.Tensor, weight: torch.Tensor, b_mn_major: bool = False):
+        """a [M, K_local], weight [N, K_local] (or [K_local, N]); returns the [M, N] sum over ranks, the
+        same bits on every rank (each row chunk is reduced once, by its owner, and stored to all)."""
+        assert self.allreduce, "workspace was created without all-reduce output buffers"
+        M, K = a.shape
+        N = weight.shape[1] if b_mn_major else weight.shape[0]
+        assert a.dtype == torch.bfloat16 and a.stride(1) == 1
+        assert M <= self.max_rows and N <= self.max_n, (M, N, self.max_rows, self.max_n)
+        self.rs_calls += 1
+        s = self.rs_calls % 2
+        parts, outs = (C.c_void_p * 8)(), (C.c_void_p * 8)()
+        for r in range(self.tp):
+            parts[r] = self._parts(r, s)
+            outs[r] = self._out(r, s)
+        L.call("b200_gemm_allreduce", C.byref(self._descs[0]), parts, outs, s, a.data_ptr(), weight.data_ptr(),
+               M, N, K, int(b_mn_major), a.stride(0), weight.stride(0), L.stream_ptr())
+        # the peers overwrite this buffer two calls from now: hand the caller its own copy
+        out = _wrap(self._out(self.rank, s), M * N * 2, self.device).view(torch.bfloat16).view(M, N).clone()
+        if self.verify:
+            want = a.float() @ (weight.float() if b_mn_major else weight.float().t())
+            dist.all_reduce(want, group=self.group)
+            err = (out.float() - want).abs().max().item()
+            if not err <= 3e-2 * max(want.abs().max().item(), 1.0):
+                raise RuntimeError(f"fused GEMM all-reduce (call {self.rs_calls}, rank {self.rank}): max abs error {err}")
         return out
 
     def check(self):
@@ -201,18 +226,20 @@ class TPWorkspace:
 _WORKSPACE = None
 
 
-def get_workspace(group, max_rows, max_k, max_n):
+def get_workspace(group, max_rows, max_k, max_n, allreduce=False):
     """Process-wide workspace of the tensor-parallel group, grown on demand (collective: all
     ranks must ask for the same sizes)."""
     global _WORKSPACE
     ws = _WORKSPACE
-    if ws is None or ws.max_rows < max_rows or ws.max_k < max_k or ws.max_n < max_n:
+    if ws is None or ws.max_rows < max_rows or ws.max_k < max_k or ws.max_n < max_n \
+            or (allreduce and not ws.allreduce):
         if ws is not None:
             max_rows, max_k, max_n = max(max_rows, ws.max_rows), max(max_k, ws.max_k), max(max_n, ws.max_n)
+            allreduce = allreduce or ws.allreduce
             # every GPU of the group must have drained its kernels (they read and write the peers'
             # buffers) BEFORE anybody unmaps or frees: device sync first, then the host barrier
             torch.cuda.synchronize()
             dist.barrier(group=group)
             ws.close()
-        ws = _WORKSPACE = TPWorkspace(group, max_rows, max_k, max_n)
+        ws = _WORKSPACE = TPWorkspace(group, max_rows, max_k, max_n, allreduce)
     return ws

@@ -143,17 +143,24 @@ int b200_stage_shard(const void* src, void* stage, void* own_rows, long long byt
                      int tp, int rank, unsigned wait_value, int do_wait, unsigned* done_counter,
                      unsigned call_index, unsigned* const* signal_addrs, int n_signal, unsigned epoch,
                      cudaStream_t stream);
-int b200_comm_flag_words(int max_blocks);
+int b200_comm_flag_words(int max_blocks, int max_tn);     /* max_tn: widest reduced output / 256 columns */
 int b200_comm_shard_ready_word(int max_blocks);
 int b200_comm_consumed_word(int max_blocks);
 int b200_comm_debug_read(unsigned* out8);
-typedef struct { int tp, rank; void* peer_stage[8]; unsigned* peer_flags[8]; int max_blocks; } B200CommDesc;
-int b200_gemm_allgather(const B200CommDesc* d, void* gathered, const void* B, void* C, int M, int N, int K,
-                        int b_mn_major, long long ldb, long long ldc, unsigned epoch, cudaStream_t stream);
-int b200_gemm_rs_arrivals(int N, int tp);
+typedef struct { int tp, rank; void* peer_stage[8]; unsigned* peer_flags[8]; int max_blocks; int max_tn; } B200CommDesc;
+int b200_gemm_allgather(const B200CommDesc* d, const void* x_shard, void* gathered, const void* B, void* C,
+                        int M, int N, int K, int b_mn_major, long long ldb, long long ldc, unsigned epoch,
+                        unsigned* stage_done, cudaStream_t stream);
+/* GEMM -> reduce-scatter (megatron/core/tensor_parallel/layers.py:691-692, :285-296): partial tiles of rows
+ * another rank owns are TMA-stored into that rank's slots; the owner adds them in the epilogue of its own
+ * tiles. b200_gemm_allreduce (layers.py:694, :278-283, no sequence parallelism): the owner additionally
+ * stores every final tile into peer_out[r] ([M, N], peer-mapped) of all ranks. `set` alternates 0/1 per call. */
 int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int set, const void* A,
                              const void* B, void* out, int M, int N, int K, int b_mn_major, long long lda,
-                             long long ldb, unsigned rs_target, cudaStream_t stream);
+                             long long ldb, cudaStream_t stream);
+int b200_gemm_allreduce(const B200CommDesc* d, void* const* peer_parts, void* const* peer_out, int set,
+                        const void* A, const void* B, int M, int N, int K, int b_mn_major, long long lda,
+                        long long ldb, cudaStream_t stream);
 
 /* ---- data-parallel reduce-scatter / Adam with parameter all-gather over peer memory (csrc/dp_comm.cu) --
  * Replaces megatron/optimizer/distrib_optimizer.py:553-567 and :592-608. Buffers come from b200_symm_alloc and

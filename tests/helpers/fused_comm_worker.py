@@ -37,8 +37,8 @@ def main():
     bench = "--bench" in sys.argv
     shapes = [(512 * world, 1024, 768), (4096, 4096, 12288 // world), (4096, 4096, 22016 // world)] if world <= 4 \
         else [(256 * world, 1024, 768), (4096, 4096, 1536)]
-    ws = TPWorkspace(grp, max_rows=4096, max_k=11008, max_n=4096)
-    out = {"world": world, "ag": [], "rs": []}
+    ws = TPWorkspace(grp, max_rows=4096, max_k=11008, max_n=4096, allreduce=True)
+    out = {"world": world, "ag": [], "rs": [], "ar": []}
     torch.manual_seed(100 + rank)
     for (M, K, N) in shapes:
         rpc = M // world
@@ -99,6 +99,35 @@ def main():
                 rec["ms_fused"], rec["ms_nccl_cublas"] = timed(fused), timed(nccl)
                 rec["ms_gemm_only"] = timed(lambda: torch.matmul(a, w.t()))
             out["rs"].append(rec)
+    # all-reduce (tensor parallelism without sequence parallelism): same shapes + one ragged width
+    for (M, K, N) in rs_shapes + [(256 * world, 520, 1000)]:
+        K = K // 8 * 8
+        for b_mn in (False, True):
+            a = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+            w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+            wst = w.t().contiguous() if b_mn else w
+            errs = []
+            for it in range(3):
+                y = ws.gemm_allreduce(a, wst, b_mn)
+                ws.check()
+                ref = a.float() @ w.float().t()
+                dist.all_reduce(ref)
+                errs.append(float((y.float() - ref).abs().max() / ref.abs().max()))
+                ys = [torch.empty_like(y) for _ in range(world)]
+                dist.all_gather(ys, y)
+                assert all(torch.equal(ys[0], t) for t in ys), "all-reduce GEMM: ranks hold different bits"
+                a = (a * 0.99).contiguous()
+            rec = {"M": M, "K": K, "N": N, "b_mn": b_mn, "max_rel_err": max(errs)}
+            if bench and not b_mn and N % 256 == 0:
+                def fused():
+                    ws.gemm_allreduce(a, wst, b_mn)
+
+                def nccl():
+                    p = torch.matmul(a, w.t())
+                    dist.all_reduce(p)
+                rec["ms_fused"], rec["ms_nccl_cublas"] = timed(fused), timed(nccl)
+                rec["ms_gemm_only"] = timed(lambda: torch.matmul(a, w.t()))
+            out["ar"].append(rec)
     torch.cuda.synchronize()
     dist.barrier()
     if rank == 0:

@@ -25,6 +25,35 @@ def single():
     return run_tiny(steps=5, num_microbatches=4)
 
 
+def _fused_comm_worker(nproc):
+    import json
+    import os
+    import subprocess
+    import sys
+    from tests.helpers.launch import ROOT, free_port
+    port = str(free_port())
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+                        "--master-addr", "127.0.0.1", "--master-port", port,
+                        os.path.join(ROOT, "tests", "helpers", "fused_comm_worker.py")],
+                       capture_output=True, text=True, timeout=600, cwd=ROOT)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")]
+    assert r.returncode == 0 and lines, r.stdout[-1500:] + r.stderr[-3000:]
+    return json.loads(lines[-1][7:])
+
+
+@pytest.mark.parametrize("nproc", [2, 4, 8])
+def test_fused_collective_gemms_match_nccl(nproc):
+    """All-gather -> GEMM, GEMM -> reduce-scatter and GEMM -> all-reduce in ONE kernel each over peer
+    memory against NCCL + fp32 matmul: both operand layouts, repeated calls without barriers, a ragged
+    output width; the all-reduce result must be bit-identical on every rank."""
+    _need(nproc)
+    res = _fused_comm_worker(nproc)
+    for kind in ("ag", "rs", "ar"):
+        assert res[kind], kind
+        for rec in res[kind]:
+            assert rec["max_rel_err"] < 2e-2, (kind, rec)
+
+
 def test_tp2_sequence_parallel(single):
     _need(2)
     r = run_tiny(nproc=2, tp=2, steps=5, num_microbatches=4)

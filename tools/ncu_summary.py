@@ -61,8 +61,11 @@ def launches(src: str, dst: str, top: int = 45):
 
 
 def report(src: str, dst: str):
-    r = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True)
-    rows = list(csv.reader(r.stdout.splitlines()))
+    if src.endswith(".csv"):     # already exported on the GPU box: ncu -i x.ncu-rep --page raw --csv
+        text = open(src).read()
+    else:
+        text = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = [r for r in csv.reader(text.splitlines()) if len(r) > 10]
     hdr, units, data = rows[0], rows[1], rows[2:]
     idx = {h: i for i, h in enumerate(hdr)}
     out = [f"# ncu --set full summary of {src}", ""]

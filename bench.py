@@ -75,7 +75,7 @@ def build_arg_list(a, tp, dp):
         "--make_vocab_size_divisible_by", "128", "--synthetic_data", "--num_workers", "0",
         "--log_interval", "1000000", "--eval_iters", "0", "--eval_interval", "1000000",
     ]
-    if tp > 1:
+    if tp > 1 and not getattr(a, 'no_sp', False):
         argv.append("--sequence_parallel")
     if a.recompute:
         argv += ["--recompute_granularity", "full", "--recompute_method", "uniform"]
@@ -258,7 +258,7 @@ def run_ours(a):
     if quiet:
         sys.stdout = real_stdout
     if rank == 0:
-        custom_layout = bool(getattr(a, 'tp', 0) or getattr(a, 'pp', 1) > 1 or a.seq != 4096 or a.recompute)
+        custom_layout = bool(getattr(a, 'no_sp', False) or getattr(a, 'tp', 0) or getattr(a, 'pp', 1) > 1 or a.seq != 4096 or a.recompute)
         out = {
             "metric": ("Llama-2 7B" if a.model == "llama2-7b" else a.model) +
                       " bf16 training throughput (tokens/s, whole job, max over ranks)",
@@ -335,6 +335,7 @@ def main():
     p.add_argument("--kernels", default="auto", help="debug only: auto|off")
     p.add_argument("--fused_comm", default="auto", help="A/B only: auto|on|off (in-kernel TP collectives)")
     p.add_argument("--fused_dp", default="auto", help="A/B only: auto|on|off (in-kernel DP reduce-scatter/all-gather)")
+    p.add_argument("--no_sp", action="store_true", help="A/B only: tensor parallelism without sequence parallelism")
     p.add_argument("--torch_profile", action="store_true", help="also write gpurun_out/torch_profile_nN.md")
     p.add_argument("--profile", action="store_true", help="1 warm-up + K steps, no e2e region; for ncu, NOT a bench value")
     a = p.parse_args()

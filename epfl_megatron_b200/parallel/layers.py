@@ -273,7 +273,7 @@ def _fused_comm_ok(rows_local: int, k_gather: int, n_scatter: int, *tensors) -> 
     return ok
 
 
-def _workspace(rows_total: int, k_gather: int, n_scatter: int):
+def _workspace(rows_total: int, k_gather: int, n_scatter: int, allreduce: bool = False):
     """The group's workspace, sized once for the whole model when the global args are known
     (every gathered / scattered activation of a decoder is [s*b, hidden])."""
     from .symm import get_workspace
@@ -282,9 +282,11 @@ def _workspace(rows_total: int, k_gather: int, n_scatter: int):
         a = global_vars.get_args()
         rows_total = max(rows_total, a.seq_length * a.micro_batch_size)
         k_gather = n_scatter = max(k_gather, n_scatter, a.hidden_size)
+        # tensor parallelism without sequence parallelism: every reduction is an all-reduce
+        allreduce = allreduce or (a.tensor_model_parallel_size > 1 and not a.sequence_parallel)
     except Exception:  # noqa: BLE001 - used outside a configured run (tests, tools)
         pass
-    return get_workspace(state.get_tensor_model_parallel_group(), rows_total, k_gather, n_scatter)
+    return get_workspace(state.get_tensor_model_parallel_group(), rows_total, k_gather, n_scatter, allreduce)
 
 
 def _accumulate_wgrad(w, go2, t2, gradient_accumulation_fusion):
@@ -377,6 +379,82 @@ class _FusedRowSP(torch.autograd.Function):
         return dx.view(ctx.in_shape), gw, None
 
 
+class _FusedRowAR(torch.autograd.Function):
+    """Tensor parallelism WITHOUT sequence parallelism: [s, b, k/tp] -> x W^T with the all-reduce in the
+    GEMM kernel (the owner of a row chunk reduces it in its epilogue and stores the final tiles into
+    every rank's output) -> [s, b, h], the same bits on all ranks. Replaces matmul + NCCL all-reduce
+    (megatron/core/tensor_parallel/layers.py:694, mappings.py:13-23). Backward is local: dY is
+    replicated."""
+
+    @staticmethod
+    def forward(ctx, input, weight, gradient_accumulation_fusion):
+        K = input.shape[-1]
+        x2 = input.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        N = weight.shape[0]
+        ws = _workspace(x2.shape[0], N, N, allreduce=True)
+        out = ws.gemm_allreduce(x2, weight)                               # [M, N]
+        ctx.save_for_backward(x2, weight)
+        ctx.weight_ref = weight
+        ctx.gaf = gradient_accumulation_fusion
+        ctx.in_shape = input.shape
+        return out.view(*input.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        x2, weight = ctx.saved_tensors
+        N = grad_output.shape[-1]
+        dy2 = grad_output.reshape(-1, N)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = Fn.gemm_nn(dy2, weight)
+        gw = _accumulate_wgrad(ctx.weight_ref, dy2, x2, ctx.gaf)
+        return dx.view(ctx.in_shape), gw, None
+
+
+class _FusedColumnAR(torch.autograd.Function):
+    """ColumnParallelLinear without sequence parallelism: the forward is a local GEMM on the
+    replicated input; the backward's dgrad needs the sum over ranks (layers.py:278-283, or the
+    backward of copy_to_tensor_model_parallel_region, mappings.py:139-140): dgrad GEMM + all-reduce in
+    one kernel."""
+
+    @staticmethod
+    def forward(ctx, input, weight, gradient_accumulation_fusion):
+        K = input.shape[-1]
+        x2 = input.reshape(-1, K)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        out = Fn.gemm_nt(x2, weight)
+        ctx.save_for_backward(x2, weight)
+        ctx.weight_ref = weight
+        ctx.gaf = gradient_accumulation_fusion
+        ctx.in_shape = input.shape
+        return out.view(*input.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        x2, weight = ctx.saved_tensors
+        N = grad_output.shape[-1]
+        go2 = grad_output.reshape(-1, N)
+        if not go2.is_contiguous():
+            go2 = go2.contiguous()
+        K = weight.shape[1]
+        ws = _workspace(go2.shape[0], K, K, allreduce=True)
+        dx = ws.gemm_allreduce(go2, weight, b_mn_major=True)               # [M, K], summed over ranks
+        gw = _accumulate_wgrad(ctx.weight_ref, go2, x2, ctx.gaf)
+        return dx.view(ctx.in_shape), gw, None
+
+
+def _fused_allreduce_ok(x, weight, n_out) -> bool:
+    """Plain tensor parallelism (no sequence parallelism): rows must split into 256-row chunks per rank."""
+    if x.dim() < 2 or state.get_tensor_model_parallel_world_size() < 2:
+        return False
+    rows = x.numel() // x.shape[-1]
+    tp = state.get_tensor_model_parallel_world_size()
+    return rows % tp == 0 and _fused_comm_ok(rows // tp, 256, n_out, x, weight)
+
+
 def linear_with_grad_accumulation_and_async_allreduce(input, weight, bias, gradient_accumulation_fusion,
                                                       async_grad_allreduce,
                                                       sequence_parallel_enabled):
@@ -433,6 +511,15 @@ class ColumnParallelLinear(torch.nn.Module):
 
     def forward(self, input_):
         bias = self.bias if not self.skip_bias_add else None
+        if self.world_size > 1 and not self.sequence_parallel_enabled and torch.is_grad_enabled() \
+                and input_.requires_grad and _fused_allreduce_ok(input_, self.weight, self.input_size):
+            # dgrad GEMM + all-reduce in one kernel in the backward pass
+            out = _FusedColumnAR.apply(input_, self.weight, self.gradient_accumulation_fusion)
+            if bias is not None:
+                out = out + bias
+            if self.gather_output:
+                out = gather_from_tensor_model_parallel_region(out)
+            return out, (self.bias if self.skip_bias_add else None)
         if self.async_tensor_model_parallel_allreduce or self.sequence_parallel_enabled or self.world_size == 1:
             x = input_
         else:
@@ -495,6 +582,12 @@ class RowParallelLinear(torch.nn.Module):
                 _fused_comm_ok(x.shape[0] * x.shape[1] // self.world_size, self.output_size, self.output_size,
                                x, self.weight):
             out_ = _FusedRowSP.apply(x, self.weight, self.gradient_accumulation_fusion)
+            if not self.skip_bias_add:
+                return (out_ + self.bias if self.bias is not None else out_), None
+            return out_, self.bias
+        if self.world_size > 1 and not self.sequence_parallel_enabled and \
+                _fused_allreduce_ok(x, self.weight, self.output_size):
+            out_ = _FusedRowAR.apply(x, self.weight, self.gradient_accumulation_fusion)
             if not self.skip_bias_add:
                 return (out_ + self.bias if self.bias is not None else out_), None
             return out_, self.bias

@@ -60,6 +60,16 @@ def test_tp2_sequence_parallel(single):
     _close(r["losses"], single["losses"], 0.03)
 
 
+def test_tp2_without_sequence_parallel_fused_allreduce(single):
+    """Plain tensor parallelism: RowParallel forward and ColumnParallel dgrad run GEMM + all-reduce in one
+    kernel (parallel/layers.py _FusedRowAR / _FusedColumnAR); same loss curve as one GPU and as NCCL."""
+    _need(2)
+    fused = run_tiny(nproc=2, tp=2, no_sp=True, steps=5, num_microbatches=4, fused_comm="auto")
+    nccl = run_tiny(nproc=2, tp=2, no_sp=True, steps=5, num_microbatches=4, fused_comm="off")
+    _close(fused["losses"], single["losses"], 0.03)
+    _close(fused["losses"], nccl["losses"], 0.01)
+
+
 def test_dp2_distributed_optimizer(single):
     _need(2)
     r = run_tiny(nproc=2, steps=5, dist_opt=True, num_microbatches=2)

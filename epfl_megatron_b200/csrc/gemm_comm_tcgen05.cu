@@ -585,11 +585,12 @@ B200_API int b200_comm_consumed_word(int max_blocks) { return 2 * max_blocks + 2
 // [M/tp, K]: the kernel stages the own shard for the peers, fills `gathered` (own rows copied, the
 // others pulled over NVLink) and multiplies, own rows first. epoch: 1, 2, ... per call on this
 // workspace, identical on all ranks; `d` must be the descriptor of staging buffer (epoch & 1);
-// stage_done: a local u32 counter used only by this entry point (zero at workspace creation).
+// stage_done: a local u32 counter used only by this entry point (zero at workspace creation),
+// stage_call: number of calls of this entry point on the workspace so far, this one included.
 B200_API int b200_gemm_allgather(const B200CommDesc* d, const void* x_shard, void* gathered, const void* B,
                                  void* C, int M, int N, int K, int b_mn_major, long long ldb,
                                  long long ldc, unsigned epoch, unsigned* stage_done,
-                                 cudaStream_t stream) {
+                                 unsigned stage_call, cudaStream_t stream) {
   if (!d || d->tp < 2 || d->tp > 8 || M % d->tp || !x_shard || !stage_done) return B200_ERR_BAD_ARG;
   const int rpc = M / d->tp;
   if (rpc % 256 || (K * 2) % 512 || M / 128 > d->max_blocks) return B200_ERR_UNSUPPORTED;
@@ -627,7 +628,9 @@ B200_API int b200_gemm_allgather(const B200CommDesc* d, const void* x_shard, voi
   ca.consumed_wait = epoch - 2u;       // the previous user of this staging buffer
   ca.do_consumed_wait = epoch > 2u;
   ca.stage_done = stage_done;
-  ca.stage_done_target = epoch * (unsigned)(fc::kStageWarps * kNumSMs);   // warps 2..7 of every CTA, every call
+  // warps 2..7 of every CTA add one per call of THIS entry point (stage_call = 1, 2, ...; the epoch
+  // sequence is shared with other users of the staging buffers and may skip numbers here)
+  ca.stage_done_target = stage_call * (unsigned)(fc::kStageWarps * kNumSMs);
   rc = fc::make_out_map(&ca.out_map[0], C, M, N, ldc);
   if (rc) return rc;
   return b_mn_major ? fc::launch<true>(ta, taloc, tb, C, M, N, K, ldc, ca, stream)

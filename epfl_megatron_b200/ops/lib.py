@@ -35,7 +35,13 @@ _SIGNATURES = {
     "b200_cast_f32_to_bf16": ([vp, vp, i64, vp], i32),
     "b200_softmax_fwd": ([vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp], i32),
     "b200_softmax_bwd": ([vp, vp, vp, i64, i32, f32, vp], i32),
+    "b200_ipc_export_range": ([vp, vp, vp], i32),
+    "b200_embed_fwd": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp], i32),
+    "b200_embed_bwd": ([vp, vp, i32, vp, i32, i32, i32, i64, i32, vp], i32),
     "b200_xent_stats": ([vp, vp, vp, i32, i32, i64, vp], i32),
+    "b200_xent_push_grid": ([i32], i32),
+    "b200_xent_stats_push": ([vp, vp, vp, vp, i32, i32, i32, i32, i64, vp], i32),
+    "b200_xent_combine_wait": ([vp, vp, C.c_uint, vp, vp, i32, i32, vp], i32),
     "b200_xent_combine": ([vp, vp, vp, i32, i32, vp], i32),
     "b200_xent_bwd": ([vp, vp, vp, vp, i32, i32, i64, vp], i32),
     "b200_adam_step": ([vp, vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, i32, i32, vp, vp, vp], i32),
@@ -74,7 +80,7 @@ _SIGNATURES = {
     "b200_dp_wait": ([vp, i32, i32, C.c_uint, C.c_uint, vp], i32),
     "b200_dp_debug_read": ([vp], i32),
     "b200_copy_async": ([vp, vp, i64, vp], i32),
-    "b200_gemm_allgather": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp, vp], i32),
+    "b200_gemm_allgather": ([vp, vp, vp, vp, vp, i32, i32, i32, i32, i64, i64, C.c_uint, vp, C.c_uint, vp], i32),
     "b200_gemm_reduce_scatter": ([vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i64, i64, vp], i32),
     "b200_gemm_allreduce": ([vp, vp, vp, i32, vp, vp, i32, i32, i32, i32, i64, i64, vp], i32),
 }
@@ -155,10 +161,25 @@ def launch_count() -> int:
     return _launches
 
 
+_SYNC_CALLS = os.environ.get("B200_SYNC_CALLS", "0") == "1"
+
+
+def _sync_check(name):
+    """B200_SYNC_CALLS=1 (debugging): wait for the device after every entry point so that an
+    asynchronous fault is reported against the kernel that caused it."""
+    import torch
+    try:
+        torch.cuda.synchronize()
+    except Exception as e:  # noqa: BLE001
+        raise KernelError(f"{name}: device fault surfaced after this call: {e}") from None
+
+
 def call(name: str, *args, launches: int = 1):
     """Invoke an entry point and turn its return code into an exception."""
     global _launches
     rc = getattr(lib(), name)(*args)
+    if _SYNC_CALLS and launches:
+        _sync_check(name)
     if rc != 0:
         if rc > 0:
             raise KernelError(f"{name}: CUDA error {rc}")

@@ -8,6 +8,8 @@ PyTorch path (CPU / fp32 / label smoothing): restatement of the reference math.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -74,6 +76,18 @@ class _VocabParallelCrossEntropyRef(torch.autograd.Function):
         return g.to(ctx.in_dtype), None, None
 
 
+def _peer_workspace(T):
+    """The tensor-parallel group's peer-memory workspace when the fused collectives are in use
+    (``--b200_fused_comm`` not off, group of 2..8 GPUs on one host), else None -> NCCL all-gather."""
+    from . import layers
+    tp = state.get_tensor_model_parallel_world_size()
+    if layers._FUSED_COMM == "off" or not (2 <= tp <= 8) or os.environ.get("B200_FUSED_XENT", "1") == "0" \
+            or not layers.tp_group_on_one_host():
+        return None
+    ws = layers._workspace(T, 256, 256)
+    return ws if T <= ws.max_rows else None
+
+
 class _VocabParallelCrossEntropyFused(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, target):
@@ -86,18 +100,23 @@ class _VocabParallelCrossEntropyFused(torch.autograd.Function):
         ws = state.get_tensor_model_parallel_world_size()
         rank = state.get_tensor_model_parallel_rank()
         lo = rank * V
-        stats = torch.empty(T, 3, device=logits.device, dtype=torch.float32)
-        L.call("b200_xent_stats", l2.data_ptr(), tgt.data_ptr(), stats.data_ptr(), T, V, lo,
-               L.stream_ptr())
-        if ws > 1:
-            allst = torch.empty(ws, T, 3, device=logits.device, dtype=torch.float32)
-            all_gather_into(allst.view(ws * T, 3), stats, state.get_tensor_model_parallel_group())
+        tpws = _peer_workspace(T) if ws > 1 else None
+        if tpws is not None:
+            # the statistics kernel stores its triples into every rank's table over NVLink
+            loss, lse = tpws.xent_exchange(l2, tgt, lo)
         else:
-            allst = stats
-        loss = torch.empty(T, device=logits.device, dtype=torch.float32)
-        lse = torch.empty(T, device=logits.device, dtype=torch.float32)
-        L.call("b200_xent_combine", allst.data_ptr(), loss.data_ptr(), lse.data_ptr(), T, ws,
-               L.stream_ptr())
+            stats = torch.empty(T, 3, device=logits.device, dtype=torch.float32)
+            L.call("b200_xent_stats", l2.data_ptr(), tgt.data_ptr(), stats.data_ptr(), T, V, lo,
+                   L.stream_ptr())
+            if ws > 1:
+                allst = torch.empty(ws, T, 3, device=logits.device, dtype=torch.float32)
+                all_gather_into(allst.view(ws * T, 3), stats, state.get_tensor_model_parallel_group())
+            else:
+                allst = stats
+            loss = torch.empty(T, device=logits.device, dtype=torch.float32)
+            lse = torch.empty(T, device=logits.device, dtype=torch.float32)
+            L.call("b200_xent_combine", allst.data_ptr(), loss.data_ptr(), lse.data_ptr(), T, ws,
+                   L.stream_ptr())
         ctx.save_for_backward(l2, tgt, lse)
         ctx.meta = (logits.shape, lo)
         return loss.view(target.shape)

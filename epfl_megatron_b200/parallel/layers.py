@@ -16,6 +16,7 @@ Public surface of megatron/core/tensor_parallel/layers.py:41-701. What differs i
 from __future__ import annotations
 
 import math
+import ctypes
 import os
 from typing import Callable, Optional
 
@@ -159,6 +160,83 @@ class _Overlap:
             torch.cuda.current_stream().wait_event(self.event)
 
 
+class _FusedVocabEmbedding(torch.autograd.Function):
+    """Vocab-parallel word embedding without a reduction (csrc/embed.cu): the forward copies every
+    output row from the table shard of the rank that owns the token (peer loads over NVLink), directly
+    in [s, b, h] order and, under sequence parallelism, only for this rank's part of the sequence; the
+    backward adds the output-gradient rows of the tokens this rank owns into the fp32 ``main_grad``
+    (rows of other sequence parts are read from the owners' staging buffers). Replaces the masked
+    lookup + all-reduce of megatron/core/tensor_parallel/layers.py:187-210 and the all-gather +
+    embedding_dense_backward + main_grad.add_ of its backward."""
+
+    @staticmethod
+    def forward(ctx, input_ids, weight, sequence_parallel):
+        tp = state.get_tensor_model_parallel_world_size()
+        rank = state.get_tensor_model_parallel_rank()
+        B, S = input_ids.shape
+        Vp, H = weight.shape
+        ids = input_ids.contiguous()
+        ws = _workspace(S * B, H, H)
+        tabs = ws.peer_tables(weight)
+        s_out = S // tp if sequence_parallel else S
+        s_off = rank * s_out if sequence_parallel else 0
+        out = torch.empty(s_out, B, H, device=weight.device, dtype=weight.dtype)
+        ws.tables_barrier()        # the peers' optimizer steps that wrote their shards are complete
+        arr = (ctypes.c_void_p * 8)(*tabs)
+        Fn.L.call("b200_embed_fwd", ids.data_ptr(), arr, out.data_ptr(), S, B, s_off, s_out, H, Vp, tp,
+                  Fn.L.stream_ptr())
+        ctx.save_for_backward(ids)
+        ctx.weight_ref = weight
+        ctx.sp = sequence_parallel
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        w = ctx.weight_ref
+        tp = state.get_tensor_model_parallel_world_size()
+        rank = state.get_tensor_model_parallel_rank()
+        B, S = ids.shape
+        Vp, H = w.shape
+        g = dout.reshape(-1, H)
+        if not g.is_contiguous():
+            g = g.contiguous()
+        main = w.main_grad
+        if getattr(w, "_b200_main_grad_empty", False):
+            main.zero_()
+            w._b200_main_grad_empty = False
+        st = Fn.L.stream_ptr()
+        if ctx.sp:
+            ws = _workspace(S * B, H, H)
+            e, srcs = ws.gather_begin(g)
+            arr = (ctypes.c_void_p * 8)(*srcs)
+            Fn.L.call("b200_embed_bwd", ids.data_ptr(), arr, tp, main.data_ptr(), S, B, H, rank * Vp, Vp, st)
+            ws.gather_end(e)
+        else:
+            arr = (ctypes.c_void_p * 8)(g.data_ptr())
+            Fn.L.call("b200_embed_bwd", ids.data_ptr(), arr, 1, main.data_ptr(), S, B, H, rank * Vp, Vp, st)
+        Fn._notify_grad_ready(w)
+        return None, None, None
+
+
+def fused_vocab_embedding_ok(input_ids, weight, sequence_parallel) -> bool:
+    """Peer-memory embedding: bf16 table with an fp32 main_grad (local DDP buffers), tensor-parallel
+    group of 2..8 GPUs on one host, equal vocabulary shards."""
+    tp = state.get_tensor_model_parallel_world_size()
+    if tp < 2 or tp > 8 or _FUSED_COMM == "off" or not Fn.kernels_enabled() \
+            or os.environ.get("B200_FUSED_EMBED", "1") == "0":      # A/B switch
+        return False
+    main = getattr(weight, "main_grad", None)
+    ok = (weight.is_cuda and weight.dtype == torch.bfloat16 and weight.shape[1] % 8 == 0 and input_ids.dim() == 2
+          and input_ids.dtype == torch.int64 and main is not None and main.dtype == torch.float32
+          and getattr(weight, "_b200_fuse_wgrad", False) and weight.is_contiguous() and main.is_contiguous()
+          and (not sequence_parallel or input_ids.shape[1] % tp == 0))
+    if ok and sequence_parallel:
+        B, S = input_ids.shape
+        ok = (S // tp) * B * weight.shape[1] * 2 <= _workspace(S * B, weight.shape[1], weight.shape[1]).stage_bytes
+    return ok and tp_group_on_one_host()
+
+
 class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
     @staticmethod
     def forward(ctx, input, weight, bias, gradient_accumulation_fusion, async_grad_allreduce,
@@ -259,6 +337,19 @@ def set_fused_comm_mode(mode: str):
     _FUSED_COMM = mode
 
 
+_TP_ONE_HOST = None
+
+
+def tp_group_on_one_host() -> bool:
+    """Peer memory (CUDA IPC) only reaches the GPUs of this host. Collective over the tensor-parallel
+    group on first use (every rank gets here in the same forward pass), cached afterwards."""
+    global _TP_ONE_HOST
+    if _TP_ONE_HOST is None:
+        from .dp_symm import group_on_one_host
+        _TP_ONE_HOST = group_on_one_host(state.get_tensor_model_parallel_group())
+    return _TP_ONE_HOST
+
+
 def _fused_comm_ok(rows_local: int, k_gather: int, n_scatter: int, *tensors) -> bool:
     """rows_local: rows of the sequence shard; k_gather: width of the gathered operand;
     n_scatter: width of the reduce-scattered result."""
@@ -267,6 +358,7 @@ def _fused_comm_ok(rows_local: int, k_gather: int, n_scatter: int, *tensors) -> 
     ok = (all(t.is_cuda and t.dtype == torch.bfloat16 for t in tensors)
           and rows_local % 256 == 0 and k_gather % 256 == 0 and n_scatter % 8 == 0
           and 2 <= state.get_tensor_model_parallel_world_size() <= 8)
+    ok = ok and tp_group_on_one_host()
     if not ok and _FUSED_COMM == "on":
         raise RuntimeError(f"--b200_fused_comm on: unsupported shape rows/rank {rows_local}, "
                            f"gathered width {k_gather}, scattered width {n_scatter}")

@@ -39,6 +39,9 @@ def _wrap(ptr: int, nbytes: int, device) -> torch.Tensor:
     return torch.as_tensor(_Mem(), device=device)
 
 
+_OPENED = {}     # CUDA IPC handle -> mapped base address (a process opens an allocation once)
+
+
 class TPWorkspace:
     """max_rows: largest M (= s*b) of a gathered activation; max_k / max_n: widest gathered input /
     reduce-scattered output in elements."""
@@ -58,12 +61,17 @@ class TPWorkspace:
         words = lib.b200_comm_flag_words(self.max_blocks, self.max_tn)
         self.w_ready = lib.b200_comm_shard_ready_word(self.max_blocks)
         self.w_consumed = lib.b200_comm_consumed_word(self.max_blocks)
-        self.w_stage_done = words            # one extra word: completion counter of the staging kernel
-        self.flag_bytes = ((words + 1) * 4 + 4095) // 4096 * 4096
+        self.w_stage_done = words            # one extra word: completion counter of the staging warps
+        self.w_xent_cnt = words + 1          # two words: arrival counters of the cross-entropy exchange
+        self.w_stage_done2 = words + 3       # completion counter of the stand-alone staging kernel
+        self.w_table_ready = words + 8       # [8] "rank r's embedding table is final for call n"
+        self.flag_bytes = ((words + 16) * 4 + 4095) // 4096 * 4096
         self.stage_bytes = (rpc * max_k * 2 + 4095) // 4096 * 4096
         self.parts_bytes = (self.tp * rpc * max_n * 2 + 4095) // 4096 * 4096
         self.out_bytes = (max_rows * max_n * 2 + 4095) // 4096 * 4096 if allreduce else 0
-        self.nbytes = self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes + 2 * self.out_bytes
+        self.xent_bytes = (self.tp * max_rows * 3 * 4 + 4095) // 4096 * 4096
+        self.nbytes = (self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes + 2 * self.out_bytes
+                       + 2 * self.xent_bytes)
         base = C.c_void_p()
         L.call("b200_symm_alloc", self.nbytes, C.byref(base), launches=0)
         self.base = base.value
@@ -84,6 +92,12 @@ class TPWorkspace:
         dist.barrier(group=group)
         self.ag_epoch = 0
         self.rs_calls = 0
+        self.xent_calls = 0
+        self._xent_target = [0, 0]
+        self.stage_calls = 0
+        self.ag_gemm_calls = 0
+        self.table_calls = 0
+        self._tables = {}
         self._descs = [self._make_desc(i) for i in range(2)]
         self._flags = _wrap(self.base, self.flag_bytes, self.device).view(torch.int32)
         # Debug modes. B200_COMM_POISON=1: after every reduce-scatter the
@@ -104,6 +118,10 @@ class TPWorkspace:
 
     def _out(self, r, s):
         return self.peer_base[r] + self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes + s * self.out_bytes
+
+    def _xent(self, r, s):
+        return (self.peer_base[r] + self.flag_bytes + 2 * self.stage_bytes + 2 * self.parts_bytes
+                + 2 * self.out_bytes + s * self.xent_bytes)
 
     def _flag(self, r, word):
         return self.peer_base[r] + 4 * word
@@ -126,6 +144,7 @@ class TPWorkspace:
         assert x_shard.is_contiguous() and x_shard.dtype == torch.bfloat16
         assert M <= self.max_rows and K <= self.max_k, (M, K, self.max_rows, self.max_k)
         self.ag_epoch += 1
+        self.ag_gemm_calls += 1
         e = self.ag_epoch
         stage = e % 2
         st = L.stream_ptr()
@@ -136,7 +155,7 @@ class TPWorkspace:
         # peers' shard_ready flags and pull the other chunks while the own rows are multiplied
         L.call("b200_gemm_allgather", C.byref(self._descs[stage]), x_shard.data_ptr(), gathered.data_ptr(),
                weight.data_ptr(), out.data_ptr(), M, N, K, int(b_mn_major), weight.stride(0), N, e,
-               self._flag(self.rank, self.w_stage_done), st)
+               self._flag(self.rank, self.w_stage_done), self.ag_gemm_calls, st)
         if self.verify:
             ref = torch.empty_like(gathered)
             dist.all_gather_into_tensor(ref, x_shard, group=self.group)
@@ -203,6 +222,115 @@ class TPWorkspace:
             if not err <= 3e-2 * max(want.abs().max().item(), 1.0):
                 raise RuntimeError(f"fused GEMM all-reduce (call {self.rs_calls}, rank {self.rank}): max abs error {err}")
         return out
+
+    # ---- staged all-gather window for kernels that pull rows themselves ----------------------
+    def gather_begin(self, x_shard: torch.Tensor):
+        """Make ``x_shard`` [rows, K] (same shape on every rank) readable by the peers and wait until the
+        peers' shards are readable here. Returns (epoch, [address of rank r's rows]); the caller's
+        kernel reads them and then calls ``gather_end(epoch)``. Shares the staging buffers and the
+        epoch sequence of ``allgather_gemm``."""
+        rows, K = x_shard.shape
+        nbytes = rows * K * 2
+        assert x_shard.is_contiguous() and x_shard.dtype == torch.bfloat16 and nbytes <= self.stage_bytes
+        self.ag_epoch += 1
+        self.stage_calls += 1
+        e = self.ag_epoch
+        stage = e % 2
+        st = L.stream_ptr()
+        addrs = (C.c_void_p * 8)()
+        n = 0
+        for r in range(self.tp):
+            if r != self.rank:
+                addrs[n] = self._flag(r, self.w_ready + self.rank)      # rank r's shard_ready[me]
+                n += 1
+        mine = self._stage(self.rank, stage)
+        L.call("b200_stage_shard", x_shard.data_ptr(), mine, mine, nbytes, self._flag(self.rank, self.w_consumed),
+               self.tp, self.rank, (e - 2) & 0xFFFFFFFF, int(e > 2), self._flag(self.rank, self.w_stage_done2),
+               self.stage_calls, addrs, n, e, st)
+        # the fused all-gather GEMM of the next epoch expects its counter set zeroed by this epoch
+        nxt = (e & 1) ^ 1
+        mb = self.max_blocks
+        self._flags[nxt * mb:(nxt + 1) * mb].zero_()
+        self._flags[2 * mb + 8 + nxt * 8:2 * mb + 16 + nxt * 8].zero_()
+        L.call("b200_symm_wait", self._flag(self.rank, self.w_ready), self.tp, self.rank, e, st)
+        srcs = [x_shard.data_ptr() if r == self.rank else self._stage(r, stage) for r in range(self.tp)]
+        return e, srcs
+
+    def gather_end(self, e: int):
+        """Tell the peers this rank has finished reading their staging buffers of epoch ``e``."""
+        addrs = (C.c_void_p * 8)()
+        n = 0
+        for r in range(self.tp):
+            if r != self.rank:
+                addrs[n] = self._flag(r, self.w_consumed + self.rank)   # rank r's consumed[me]
+                n += 1
+        L.call("b200_symm_signal", addrs, n, e, L.stream_ptr())
+
+    # ---- vocab-parallel embedding tables ------------------------------------------------------
+    def peer_tables(self, weight: torch.Tensor):
+        """Addresses of every rank's shard of an embedding table in THIS rank's address space (CUDA IPC
+        mapping of the allocation that holds the parameter; collective on first use per parameter)."""
+        key = (weight.data_ptr(), weight.numel())
+        tabs = self._tables.get(key)
+        if tabs is None:
+            handle = (C.c_ubyte * 64)()
+            off = C.c_longlong()
+            L.call("b200_ipc_export_range", weight.data_ptr(), handle, C.byref(off), launches=0)
+            infos = [None] * self.tp
+            dist.all_gather_object(infos, (bytes(handle), off.value), group=self.group)
+            tabs = []
+            for r, (h, o) in enumerate(infos):
+                if r == self.rank:
+                    tabs.append(weight.data_ptr())
+                    continue
+                base = _OPENED.get(h)
+                if base is None:
+                    p = C.c_void_p()
+                    L.call("b200_symm_import", (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p), launches=0)
+                    base = _OPENED[h] = p.value
+                tabs.append(base + o)
+            self._tables[key] = tabs
+        return tabs
+
+    def tables_barrier(self):
+        """Stream-ordered handshake of the group: after it, every peer's kernels enqueued before ITS
+        call (the optimizer step that wrote the table) are complete. One flag store per peer + one
+        wait kernel."""
+        self.table_calls += 1
+        n_call = self.table_calls
+        st = L.stream_ptr()
+        addrs = (C.c_void_p * 8)()
+        n = 0
+        for r in range(self.tp):
+            if r != self.rank:
+                addrs[n] = self._flag(r, self.w_table_ready + self.rank)
+                n += 1
+        L.call("b200_symm_signal", addrs, n, n_call & 0xFFFFFFFF, st)
+        L.call("b200_symm_wait", self._flag(self.rank, self.w_table_ready), self.tp, self.rank,
+               n_call & 0xFFFFFFFF, st)
+
+    # ---- vocab-parallel cross entropy: exchange of (max, sum-exp, target logit) ---------------
+    def xent_exchange(self, logits2d: torch.Tensor, labels: torch.Tensor, vocab_start: int):
+        """logits2d [T, V/tp] bf16, labels [T] int64 (global ids) -> (loss [T], lse [T]) fp32. The
+        statistics kernel stores its triples into every rank's table and the combine kernel waits for
+        all of them: two launches, no collective call."""
+        T, V = logits2d.shape
+        assert T <= self.max_rows, (T, self.max_rows)
+        self.xent_calls += 1
+        s = self.xent_calls % 2
+        stats, cnts = (C.c_void_p * 8)(), (C.c_void_p * 8)()
+        for r in range(self.tp):
+            stats[r] = self._xent(r, s)
+            cnts[r] = self._flag(r, self.w_xent_cnt + s)
+        st = L.stream_ptr()
+        L.call("b200_xent_stats_push", logits2d.data_ptr(), labels.data_ptr(), stats, cnts, self.tp, self.rank,
+               T, V, vocab_start, st)
+        self._xent_target[s] = (self._xent_target[s] + self.tp * L.lib().b200_xent_push_grid(T)) & 0xFFFFFFFF
+        loss = torch.empty(T, device=self.device, dtype=torch.float32)
+        lse = torch.empty(T, device=self.device, dtype=torch.float32)
+        L.call("b200_xent_combine_wait", self._xent(self.rank, s), self._flag(self.rank, self.w_xent_cnt + s),
+               self._xent_target[s], loss.data_ptr(), lse.data_ptr(), T, self.tp, st)
+        return loss, lse
 
     def check(self):
         """Synchronise and raise if a cross-GPU wait timed out since the last check (debug / tests)."""

@@ -92,6 +92,15 @@ int b200_xent_stats(const void* logits, const long long* labels, float* stats, i
                     long long vocab_start, cudaStream_t stream);
 int b200_xent_combine(const float* all_stats, float* loss, float* lse, int T, int tp,
                       cudaStream_t stream);
+/* Exchange inside the kernels (tensor-parallel group on one NVSwitch domain): the statistics pass stores its
+ * triples into every rank's peer-mapped table and counts itself in there; the combine waits for `target`
+ * arrivals (running total: tp * b200_xent_push_grid(T) per call on that counter). */
+int b200_xent_push_grid(int T);
+int b200_xent_stats_push(const void* logits, const long long* labels, float* const* peer_stats,
+                         unsigned* const* peer_cnt, int tp, int rank, int T, int V, long long vocab_start,
+                         cudaStream_t stream);
+int b200_xent_combine_wait(const float* all_stats, const unsigned* cnt, unsigned target, float* loss, float* lse,
+                           int T, int tp, cudaStream_t stream);
 int b200_xent_bwd(void* logits, const long long* labels, const float* lse, const float* dloss,
                   int T, int V, long long vocab_start, cudaStream_t stream);
 
@@ -150,7 +159,7 @@ int b200_comm_debug_read(unsigned* out8);
 typedef struct { int tp, rank; void* peer_stage[8]; unsigned* peer_flags[8]; int max_blocks; int max_tn; } B200CommDesc;
 int b200_gemm_allgather(const B200CommDesc* d, const void* x_shard, void* gathered, const void* B, void* C,
                         int M, int N, int K, int b_mn_major, long long ldb, long long ldc, unsigned epoch,
-                        unsigned* stage_done, cudaStream_t stream);
+                        unsigned* stage_done, unsigned stage_call, cudaStream_t stream);
 /* GEMM -> reduce-scatter (megatron/core/tensor_parallel/layers.py:691-692, :285-296): partial tiles of rows
  * another rank owns are TMA-stored into that rank's slots; the owner adds them in the epilogue of its own
  * tiles. b200_gemm_allreduce (layers.py:694, :278-283, no sequence parallelism): the owner additionally
@@ -161,6 +170,19 @@ int b200_gemm_reduce_scatter(const B200CommDesc* d, void* const* peer_parts, int
 int b200_gemm_allreduce(const B200CommDesc* d, void* const* peer_parts, void* const* peer_out, int set,
                         const void* A, const void* B, int M, int N, int K, int b_mn_major, long long lda,
                         long long ldb, cudaStream_t stream);
+
+/* ---- vocab-parallel embedding over peer memory (csrc/embed.cu) -------------------------------------------
+ * Replaces megatron/core/tensor_parallel/layers.py:187-210 (masked local lookup + all-reduce) and its backward.
+ * b200_ipc_export_range: CUDA IPC handle of the allocation containing `ptr` + the offset of `ptr` inside it.
+ * b200_embed_fwd: out[(si - s_off) * B + bi] = tables[id / Vp][id % Vp], id = ids[bi * S + si] (ids [B, S] int64,
+ *   tables[r] = rank r's [Vp, H] bf16 shard, peer-mapped); out is [s_out * B, H] in [s, b, h] order.
+ * b200_embed_bwd: main_grad[id - lo] (fp32 [Vp, H]) += output-gradient row of every token with lo <= id < lo + Vp;
+ *   srcs[c] = rows of sequence chunk c (local tensor or a peer's staging buffer), vector atomics. */
+int b200_ipc_export_range(const void* ptr, void* handle64, long long* offset_out);
+int b200_embed_fwd(const long long* ids, const void* const* tables, void* out, int S, int B, int s_off, int s_out,
+                   int H, int Vp, int tp, cudaStream_t stream);
+int b200_embed_bwd(const long long* ids, const void* const* srcs, int n_chunks, float* main_grad, int S, int B,
+                   int H, long long lo, int Vp, cudaStream_t stream);
 
 /* ---- data-parallel reduce-scatter / Adam with parameter all-gather over peer memory (csrc/dp_comm.cu) --
  * Replaces megatron/optimizer/distrib_optimizer.py:553-567 and :592-608. Buffers come from b200_symm_alloc and

@@ -70,6 +70,20 @@ def test_tp2_without_sequence_parallel_fused_allreduce(single):
     _close(fused["losses"], nccl["losses"], 0.01)
 
 
+def test_tp2_tied_gpt_peer_memory_embedding_and_cross_entropy():
+    """Tied GPT under TP2 + SP: the word embedding is read from the owning rank's table shard and its
+    gradient accumulated into main_grad by own kernels (twice per micro-batch: lookup + LM head), the
+    cross-entropy statistics travel by peer stores. Same losses as one GPU and as the NCCL path."""
+    _need(2)
+    kw = dict(steps=5, model_name="gpt", num_microbatches=2)
+    one = run_tiny(**kw)
+    fused = run_tiny(nproc=2, tp=2, **kw)
+    nccl = run_tiny(nproc=2, tp=2, fused_comm="off", **kw)
+    _close(fused["losses"], one["losses"], 0.03)
+    _close(fused["losses"], nccl["losses"], 0.01)
+    _close(fused["grad_norms"], nccl["grad_norms"], 0.05)
+
+
 def test_dp2_distributed_optimizer(single):
     _need(2)
     r = run_tiny(nproc=2, steps=5, dist_opt=True, num_microbatches=2)

@@ -339,37 +339,63 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const long long segs_per_block = (long long)kBM * (ca.row_bytes / 512);  // 512 B = one warp access
       const int nrb = ca.rows_per_chunk / kBM;
       stage_own_rows(ca, blockIdx.x * kStageWarps + (warp - 2), lane);
-      for (int step = 1; step < ca.tp; ++step) {
+      // Flat, software-pipelined pull: a unit = one pass of all copier warps over (part of) a 128-row
+      // block of a remote chunk, chunks in the order the tiles need them. The loads of unit u+1 are in
+      // flight (second register buffer) while unit u is stored, fenced and counted, so the NVLink
+      // round trip is paid once per warp instead of once per block: at tp 8 the 14 blocks of a
+      // 2048-row activation no longer queue behind each other.
+      constexpr int U = 16;         // 16 x 512 B per warp and buffer: 2 x 2.4 MB in flight over the grid
+      const long long per_pass = (long long)nw * U;
+      const int sub_per_block = (int)((segs_per_block + per_pass - 1) / per_pass);
+      const int units = (ca.tp - 1) * nrb * sub_per_block;
+      const long long chunk_vec = (long long)ca.rows_per_chunk * (ca.row_bytes / 16);
+      auto issue = [&](int unit, uint4* v) {
+        const int blk = unit / sub_per_block, sub = unit - blk * sub_per_block;
+        const int step = blk / nrb + 1, rb = blk - (step - 1) * nrb;
         const int src = (ca.rank + step) % ca.tp;
-        if (lane == 0) spin_until<true>(&ca.shard_ready[src], ca.epoch, 2u, src, ca.epoch, ca.mode, ca.rank);
-        __syncwarp();
-        const uint4* s = ca.peer_src[src] + lane;
-        uint4* d = ca.gathered + (long long)src * ca.rows_per_chunk * (ca.row_bytes / 16) + lane;
-        for (int rb = 0; rb < nrb; ++rb) {
-          const long long base = (long long)rb * segs_per_block;
-          constexpr int U = 16;   // 16 x 512 B per warp in flight: ~2.4 MB over the whole grid
-          for (long long sg = w; sg < segs_per_block; sg += (long long)nw * U) {
-            uint4 v[U];
+        if (sub == 0 && rb == 0) {
+          if (lane == 0) spin_until<true>(&ca.shard_ready[src], ca.epoch, 2u, src, ca.epoch, ca.mode, ca.rank);
+          __syncwarp();
+        }
+        const uint4* sp = ca.peer_src[src] + lane + (long long)rb * segs_per_block * 32;
+        const long long g0 = (long long)sub * per_pass + w;
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-              const long long g = sg + (long long)u * nw;
-              if (g < segs_per_block) v[u] = __ldcv(s + (base + g) * 32);
-            }
+        for (int u = 0; u < U; ++u) {
+          const long long g = g0 + (long long)u * nw;
+          if (g < segs_per_block) v[u] = __ldcv(sp + g * 32);
+        }
+      };
+      auto retire = [&](int unit, const uint4* v) {
+        const int blk = unit / sub_per_block, sub = unit - blk * sub_per_block;
+        const int step = blk / nrb + 1, rb = blk - (step - 1) * nrb;
+        const int src = (ca.rank + step) % ca.tp;
+        uint4* dp = ca.gathered + (long long)src * chunk_vec + lane + (long long)rb * segs_per_block * 32;
+        const long long g0 = (long long)sub * per_pass + w;
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-              const long long g = sg + (long long)u * nw;
-              if (g < segs_per_block) d[(base + g) * 32] = v[u];
-            }
-          }
+        for (int u = 0; u < U; ++u) {
+          const long long g = g0 + (long long)u * nw;
+          if (g < segs_per_block) dp[g * 32] = v[u];
+        }
+        if (sub == sub_per_block - 1) {
           fence_proxy_async_global();   // the rows are read back by TMA (async proxy)
           __syncwarp();
-          if (lane == 0) red_release_gpu_add(&ca.row_ready[src * nrb + rb], 1u);
+          if (lane == 0) {
+            red_release_gpu_add(&ca.row_ready[src * nrb + rb], 1u);
+            if (rb == nrb - 1) {
+              __threadfence();
+              const unsigned old = atomicAdd(&ca.chunk_done[src], 1u);
+              if (old + 1u == (unsigned)nw) st_release_sys(ca.peer_consumed[src], ca.epoch);
+            }
+          }
         }
-        if (lane == 0) {
-          __threadfence();
-          const unsigned old = atomicAdd(&ca.chunk_done[src], 1u);
-          if (old + 1u == (unsigned)nw) st_release_sys(ca.peer_consumed[src], ca.epoch);
-        }
+      };
+      uint4 va[U], vb[U];
+      if (units > 0) issue(0, va);
+      for (int unit = 0; unit < units; unit += 2) {
+        if (unit + 1 < units) issue(unit + 1, vb);
+        retire(unit, va);
+        if (unit + 2 < units) issue(unit + 2, va);
+        if (unit + 1 < units) retire(unit + 1, vb);
       }
     }
   } else if (warp >= 4) {
@@ -420,19 +446,27 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           float pacc[32];
 #pragma unroll
           for (int k = 0; k < 32; ++k) pacc[k] = 0.f;
-          for (int p = 0; p < ca.tp; ++p) {
-            if (p == ca.rank) continue;
-            const uint4* src = reinterpret_cast<const uint4*>(prow + (size_t)p * slot + c * 32);
-            uint4 q[4];
+          // four peers' loads are issued together (one L2 / HBM round trip per batch, not per peer)
+          for (int pb = 0; pb < ca.tp; pb += 4) {
+            uint4 q[4][4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              q[j] = (n0 + c * 32 + j * 8 < N) ? __ldcv(src + j) : make_uint4(0u, 0u, 0u, 0u);
+            for (int i = 0; i < 4; ++i) {
+              const int p = pb + i;
+              const bool on = p < ca.tp && p != ca.rank;
+              const uint4* src = reinterpret_cast<const uint4*>(prow + (size_t)(on ? p : 0) * slot + c * 32);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float f[8];
-              unpack8(q[j], f);
+              for (int j = 0; j < 4; ++j)
+                q[i][j] = (on && n0 + c * 32 + j * 8 < N) ? __ldcv(src + j) : make_uint4(0u, 0u, 0u, 0u);
+            }
 #pragma unroll
-              for (int k = 0; k < 8; ++k) pacc[j * 8 + k] += f[k];
+            for (int i = 0; i < 4; ++i) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float f[8];
+                unpack8(q[i][j], f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) pacc[j * 8 + k] += f[k];
+              }
             }
           }
           tmem_ld_wait();

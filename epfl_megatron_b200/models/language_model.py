@@ -126,14 +126,14 @@ class Embedding(MegatronModule):
     def forward(self, input_ids, position_ids, tokentype_ids=None):
         tp = mpu.get_tensor_model_parallel_world_size()
         extra = (self.position_embeddings is not None) or (tokentype_ids is not None)
-        if tp > 1 and not extra and torch.is_grad_enabled() and \
+        if not extra and torch.is_grad_enabled() and input_ids.is_cuda and \
                 tp_layers.fused_vocab_embedding_ok(input_ids, self.word_embeddings.weight, self.sequence_parallel):
             # rows copied straight from the owning rank's table shard over peer memory: no reduction
             emb = tp_layers._FusedVocabEmbedding.apply(input_ids, self.word_embeddings.weight,
                                                        self.sequence_parallel)
             if self.fp32_residual_connection:
                 emb = emb.float()
-            if self.sequence_parallel:
+            if self.sequence_parallel and tp > 1:
                 with tp_random.get_cuda_rng_tracker().fork():
                     return self.embedding_dropout(emb)
             return self.embedding_dropout(emb)

@@ -176,12 +176,16 @@ class _FusedVocabEmbedding(torch.autograd.Function):
         B, S = input_ids.shape
         Vp, H = weight.shape
         ids = input_ids.contiguous()
-        ws = _workspace(S * B, H, H)
-        tabs = ws.peer_tables(weight)
+        sequence_parallel = sequence_parallel and tp > 1
         s_out = S // tp if sequence_parallel else S
         s_off = rank * s_out if sequence_parallel else 0
         out = torch.empty(s_out, B, H, device=weight.device, dtype=weight.dtype)
-        ws.tables_barrier()        # the peers' optimizer steps that wrote their shards are complete
+        if tp > 1:
+            ws = _workspace(S * B, H, H)
+            tabs = ws.peer_tables(weight)
+            ws.tables_barrier()    # the peers' optimizer steps that wrote their shards are complete
+        else:
+            tabs = [weight.data_ptr()]
         arr = (ctypes.c_void_p * 8)(*tabs)
         Fn.L.call("b200_embed_fwd", ids.data_ptr(), arr, out.data_ptr(), S, B, s_off, s_out, H, Vp, tp,
                   Fn.L.stream_ptr())
@@ -220,10 +224,11 @@ class _FusedVocabEmbedding(torch.autograd.Function):
 
 
 def fused_vocab_embedding_ok(input_ids, weight, sequence_parallel) -> bool:
-    """Peer-memory embedding: bf16 table with an fp32 main_grad (local DDP buffers), tensor-parallel
-    group of 2..8 GPUs on one host, equal vocabulary shards."""
+    """Own embedding kernels: bf16 table with an fp32 main_grad (local DDP buffers); with tensor
+    parallelism a group of 2..8 GPUs on one host with equal vocabulary shards (peer memory). On one GPU
+    the same kernels copy the rows in [s, b, h] order and scatter-add the gradient into main_grad."""
     tp = state.get_tensor_model_parallel_world_size()
-    if tp < 2 or tp > 8 or _FUSED_COMM == "off" or not Fn.kernels_enabled() \
+    if tp > 8 or (tp > 1 and _FUSED_COMM == "off") or not Fn.kernels_enabled() \
             or os.environ.get("B200_FUSED_EMBED", "1") == "0":      # A/B switch
         return False
     main = getattr(weight, "main_grad", None)
@@ -231,10 +236,10 @@ def fused_vocab_embedding_ok(input_ids, weight, sequence_parallel) -> bool:
           and input_ids.dtype == torch.int64 and main is not None and main.dtype == torch.float32
           and getattr(weight, "_b200_fuse_wgrad", False) and weight.is_contiguous() and main.is_contiguous()
           and (not sequence_parallel or input_ids.shape[1] % tp == 0))
-    if ok and sequence_parallel:
+    if ok and sequence_parallel and tp > 1:
         B, S = input_ids.shape
         ok = (S // tp) * B * weight.shape[1] * 2 <= _workspace(S * B, weight.shape[1], weight.shape[1]).stage_bytes
-    return ok and tp_group_on_one_host()
+    return ok and (tp == 1 or tp_group_on_one_host())
 
 
 class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):

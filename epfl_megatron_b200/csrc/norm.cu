@@ -301,6 +301,12 @@ int rmsnorm_bwd_tma(const void* dy, const void* x, const void* w, const float* r
                     void* dx, float* dw, float* scratch, int M, int H, int accumulate,
                     cudaStream_t stream);
 
+int layernorm_fwd_tma(const void* x, const void* w, const void* b, void* y, float* mean, float* rstd, int M,
+                      int H, float eps, cudaStream_t stream);
+int layernorm_bwd_tma(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,
+                      void* dx, float* dgamma, float* dbeta, float* scratch, int M, int H, int accumulate,
+                      cudaStream_t stream);
+
 // B200_NORM_IMPL = tma (default: bulk-copy ring, csrc/norm_tma.cu) | warp | block: A/B switch for
 // tools/kernel_bench.py, read once.
 static int norm_impl() {
@@ -377,6 +383,7 @@ B200_API int b200_rmsnorm_bwd(const void* dy, const void* x, const void* w, cons
 B200_API int b200_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* mean,
                                 float* rstd, int M, int H, float eps, cudaStream_t stream) {
   if (!norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
+  if (norm_impl() == 0 && rmsnorm_tma_ok(M, H)) return layernorm_fwd_tma(x, w, b, y, mean, rstd, M, H, eps, stream);
   int grid = M < 8 * kNumSMs ? M : 8 * kNumSMs;
   layernorm_fwd_kernel<<<grid, kNormThreads, 0, stream>>>(
       (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, (const __nv_bfloat16*)b,
@@ -391,6 +398,8 @@ B200_API int b200_layernorm_bwd(const void* dy, const void* x, const void* w, co
                                 float* scratch, int M, int H, int accumulate,
                                 cudaStream_t stream) {
   if (!norm_shape_ok(M, H)) return B200_ERR_UNSUPPORTED;
+  if (norm_impl() == 0 && rmsnorm_tma_ok(M, H))
+    return layernorm_bwd_tma(dy, x, w, mean, rstd, dx, dgamma, dbeta, scratch, M, H, accumulate, stream);
   int grid = b200_norm_bwd_grid(M);
   layernorm_bwd_kernel<<<grid, kNormThreads, 0, stream>>>(
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, mean, rstd,

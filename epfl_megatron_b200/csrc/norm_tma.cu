@@ -33,7 +33,7 @@ constexpr int kNtThreads = kNtConsumers + 32;
 constexpr int kNtRows = 2;        // rows per ring stage
 constexpr int kNtVpt = 4;         // 16-byte vectors per thread and row: H <= group threads * 4 * 8
 constexpr int kNtMaxStages = 12;
-constexpr int kNtHeader = 1024;   // barriers + reduction scratch
+constexpr int kNtHeader = 2048;   // barriers + reduction scratch
 constexpr int kNtSmemBudget = 200 * 1024;
 
 __device__ __forceinline__ void nt_bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes,
@@ -54,6 +54,7 @@ struct NtSmem {
   uint64_t full[kNtMaxStages];
   uint64_t empty[kNtMaxStages];
   float red[4][2][kNtRows][8];    // [group][parity][row][warp of the group]
+  float red2[4][2][kNtRows][8];   // second per-row sum of the LayerNorm kernels
 };
 static_assert(sizeof(NtSmem) <= kNtHeader, "header too small");
 
@@ -89,6 +90,45 @@ __device__ __forceinline__ void nt_produce(NtSmem* sm, uint8_t* stages, const __
     nt_bulk_load(dst, a0 + (size_t)r0 * H, bytes, &sm->full[slot]);
     if (kArrays > 1) nt_bulk_load(dst + kNtRows * row_bytes, a1 + (size_t)r0 * H, bytes, &sm->full[slot]);
     if (kArrays > 2) nt_bulk_load(dst + 2 * kNtRows * row_bytes, a2 + (size_t)r0 * H, bytes, &sm->full[slot]);
+  }
+}
+
+// Fold the consumer groups' per-column partial sums in group order (fixed order: deterministic)
+// through `fold` (idle ring memory, >= H floats) and write the CTA's row of the [grid, .., H] scratch.
+// Called by all consumer threads after their last stage.
+template <int kGW>
+__device__ __forceinline__ void nt_fold_groups(float (&acc)[kNtVpt][8], float* fold, float* dst, int grp,
+                                               int gtid, int nvec) {
+  constexpr int kGroups = kNtConsumerWarps / kGW;
+  constexpr int kGT = kGW * 32;
+  nt_bar(kNtAllBar, kNtConsumers);
+#pragma unroll 1
+  for (int gsel = 0; gsel < kGroups; ++gsel) {
+    if (grp == gsel) {
+#pragma unroll
+      for (int i = 0; i < kNtVpt; ++i) {
+        const int v = gtid + i * kGT;
+        if (v < nvec) {
+          float4* f = reinterpret_cast<float4*>(fold + (size_t)v * 8);
+          float4 lo = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+          float4 hi = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+          if (gsel > 0) {
+            const float4 a = f[0], b = f[1];
+            lo.x += a.x; lo.y += a.y; lo.z += a.z; lo.w += a.w;
+            hi.x += b.x; hi.y += b.y; hi.z += b.z; hi.w += b.w;
+          }
+          if (gsel == kGroups - 1) {
+            float4* p = reinterpret_cast<float4*>(dst + (size_t)v * 8);
+            p[0] = lo;
+            p[1] = hi;
+          } else {
+            f[0] = lo;
+            f[1] = hi;
+          }
+        }
+      }
+    }
+    if (gsel + 1 < kGroups) nt_bar(kNtAllBar, kNtConsumers);
   }
 }
 
@@ -299,37 +339,266 @@ rmsnorm_bwd_tma_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16
     __syncwarp();
     if (lane == 0) mbar_arrive(&sm->empty[slot]);
   }
-  // Fold the groups' column partials in group order (fixed order: deterministic) through the
-  // now idle ring memory, then one row of the [grid, H] scratch per CTA.
-  float* fold = reinterpret_cast<float*>(stages);
-  nt_bar(kNtAllBar, kNtConsumers);
-#pragma unroll 1
-  for (int gsel = 0; gsel < kGroups; ++gsel) {
-    if (grp == gsel) {
+  nt_fold_groups<kGW>(dwacc, reinterpret_cast<float*>(stages), partial + (size_t)blockIdx.x * H, grp, gtid, nvec);
+}
+
+// ------------------------------- LayerNorm on the same ring -------------------------------
+// Behaviour of the reference's mixed-precision LayerNorm extension
+// (megatron/fused_kernels/layer_norm_cuda_kernel.cu: fp32 mean / variance per row, output in the
+// parameter dtype, mean and 1/std saved): y = (x - mean) * rstd * w + b, two-pass variance.
+template <int kGW>
+__global__ void __launch_bounds__(kNtThreads, 1)
+layernorm_fwd_tma_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w,
+                         const __nv_bfloat16* __restrict__ b, __nv_bfloat16* __restrict__ y,
+                         float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int H,
+                         float eps, int S, int stage_bytes) {
+  constexpr int kGroups = kNtConsumerWarps / kGW;
+  constexpr int kGT = kGW * 32;
+  extern __shared__ __align__(1024) uint8_t nt_smem[];
+  NtSmem* sm = reinterpret_cast<NtSmem*>(nt_smem);
+  uint8_t* stages = nt_smem + kNtHeader;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = H >> 3;
+  const int row_bytes = H * 2;
+  const int T = (M + kNtRows - 1) / kNtRows;
+  nt_init<kGW>(sm, S);
+  if (warp == kNtConsumerWarps) {
+    if (lane == 0) nt_produce<1>(sm, stages, x, nullptr, nullptr, M, H, T, S, stage_bytes);
+    return;
+  }
+  const int grp = warp / kGW, gwarp = warp % kGW;
+  const int gtid = threadIdx.x - grp * kGT;
+  const uint4* wvec = reinterpret_cast<const uint4*>(w);
+  const uint4* bvec = reinterpret_cast<const uint4*>(b);
+  int it = grp, par = 0;
+  for (int t = blockIdx.x + grp * gridDim.x; t < T; t += kGroups * gridDim.x, it += kGroups, par ^= 1) {
+    const int slot = it % S;
+    const uint32_t ph = (uint32_t)(it / S) & 1u;
+    const int r0 = t * kNtRows;
+    const int nr = min(kNtRows, M - r0);
+    const uint8_t* st = stages + (size_t)slot * stage_bytes;
+    mbar_wait(&sm->full[slot], ph);
+    bf16x8 hv[kNtRows][kNtVpt];
+    float s1[kNtRows];
 #pragma unroll
-      for (int i = 0; i < kNtVpt; ++i) {
-        const int v = gtid + i * kGT;
-        if (v < nvec) {
-          float4* f = reinterpret_cast<float4*>(fold + (size_t)v * 8);
-          float4 lo = make_float4(dwacc[i][0], dwacc[i][1], dwacc[i][2], dwacc[i][3]);
-          float4 hi = make_float4(dwacc[i][4], dwacc[i][5], dwacc[i][6], dwacc[i][7]);
-          if (gsel > 0) {
-            const float4 a = f[0], b = f[1];
-            lo.x += a.x; lo.y += a.y; lo.z += a.z; lo.w += a.w;
-            hi.x += b.x; hi.y += b.y; hi.z += b.z; hi.w += b.w;
-          }
-          if (gsel == kGroups - 1) {
-            float4* p = reinterpret_cast<float4*>(partial + (size_t)blockIdx.x * H + (size_t)v * 8);
-            p[0] = lo;
-            p[1] = hi;
-          } else {
-            f[0] = lo;
-            f[1] = hi;
+    for (int r = 0; r < kNtRows; ++r) {
+      s1[r] = 0.f;
+      if (r < nr) {
+        const bf16x8* xr = reinterpret_cast<const bf16x8*>(st + r * row_bytes);
+#pragma unroll
+        for (int i = 0; i < kNtVpt; ++i) {
+          const int v = gtid + i * kGT;
+          if (v < nvec) {
+            hv[r][i] = xr[v];
+            float a[8];
+            unpack8(hv[r][i], a);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s1[r] += a[k];
           }
         }
       }
     }
-    if (gsel + 1 < kGroups) nt_bar(kNtAllBar, kNtConsumers);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm->empty[slot]);     // the rows are in registers
+#pragma unroll
+    for (int r = 0; r < kNtRows; ++r) {
+      const float sr = warp_sum(s1[r]);
+      if (lane == 0) sm->red[grp][par][r][gwarp] = sr;
+    }
+    nt_bar(1 + grp, kGT);
+    float mean[kNtRows], s2[kNtRows];
+#pragma unroll
+    for (int r = 0; r < kNtRows; ++r) {
+      float tot = 0.f;
+#pragma unroll
+      for (int q = 0; q < kGW; ++q) tot += sm->red[grp][par][r][q];
+      mean[r] = tot / (float)H;
+      s2[r] = 0.f;
+      if (r < nr) {
+#pragma unroll
+        for (int i = 0; i < kNtVpt; ++i) {
+          if (gtid + i * kGT < nvec) {
+            float a[8];
+            unpack8(hv[r][i], a);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s2[r] += (a[k] - mean[r]) * (a[k] - mean[r]);
+          }
+        }
+      }
+      const float sr = warp_sum(s2[r]);
+      if (lane == 0) sm->red2[grp][par][r][gwarp] = sr;
+    }
+    nt_bar(1 + grp, kGT);
+#pragma unroll
+    for (int r = 0; r < kNtRows; ++r) {
+      if (r < nr) {
+        float tot = 0.f;
+#pragma unroll
+        for (int q = 0; q < kGW; ++q) tot += sm->red2[grp][par][r][q];
+        const float rstd = rsqrtf(tot / (float)H + eps);
+        if (gtid == 0) {
+          mean_out[r0 + r] = mean[r];
+          rstd_out[r0 + r] = rstd;
+        }
+#pragma unroll
+        for (int i = 0; i < kNtVpt; ++i) {
+          const int v = gtid + i * kGT;
+          if (v < nvec) {
+            float a[8], wf[8], bf[8], o[8];
+            unpack8(hv[r][i], a);
+            unpack8(__ldg(wvec + v), wf);
+            if (b) unpack8(__ldg(bvec + v), bf);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = (a[k] - mean[r]) * rstd * wf[k] + (b ? bf[k] : 0.f);
+            reinterpret_cast<bf16x8*>(y + (size_t)(r0 + r) * H)[v] = pack8(o);
+          }
+        }
+      }
+    }
+  }
+}
+
+// dx = rstd * (g - mean(g) - xhat * mean(g * xhat)), g = dy * w, xhat = (x - mean) * rstd;
+// partial[cta][0][c] = sum dy * xhat (dgamma), partial[cta][1][c] = sum dy (dbeta).
+template <int kGW>
+__global__ void __launch_bounds__(kNtThreads, 1)
+layernorm_bwd_tma_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                         const __nv_bfloat16* __restrict__ w, const float* __restrict__ mean_in,
+                         const float* __restrict__ rstd_in, __nv_bfloat16* __restrict__ dx,
+                         float* __restrict__ partial, int M, int H, int S, int stage_bytes) {
+  constexpr int kGroups = kNtConsumerWarps / kGW;
+  constexpr int kGT = kGW * 32;
+  extern __shared__ __align__(1024) uint8_t nt_smem[];
+  NtSmem* sm = reinterpret_cast<NtSmem*>(nt_smem);
+  uint8_t* stages = nt_smem + kNtHeader;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nvec = H >> 3;
+  const int row_bytes = H * 2;
+  const int T = (M + kNtRows - 1) / kNtRows;
+  nt_init<kGW>(sm, S);
+  if (warp == kNtConsumerWarps) {
+    if (lane == 0) nt_produce<2>(sm, stages, dy, x, nullptr, M, H, T, S, stage_bytes);
+    return;
+  }
+  const int grp = warp / kGW, gwarp = warp % kGW;
+  const int gtid = threadIdx.x - grp * kGT;
+  const uint4* wvec = reinterpret_cast<const uint4*>(w);
+  float dg[kNtVpt][8], db[kNtVpt][8];
+#pragma unroll
+  for (int i = 0; i < kNtVpt; ++i)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) dg[i][k] = db[i][k] = 0.f;
+  int it = grp, par = 0;
+  for (int t = blockIdx.x + grp * gridDim.x; t < T; t += kGroups * gridDim.x, it += kGroups, par ^= 1) {
+    const int slot = it % S;
+    const uint32_t ph = (uint32_t)(it / S) & 1u;
+    const int r0 = t * kNtRows;
+    const int nr = min(kNtRows, M - r0);
+    const uint8_t* st = stages + (size_t)slot * stage_bytes;
+    float mean[kNtRows], rstd[kNtRows];
+#pragma unroll
+    for (int r = 0; r < kNtRows; ++r) {
+      mean[r] = r < nr ? mean_in[r0 + r] : 0.f;
+      rstd[r] = r < nr ? rstd_in[r0 + r] : 0.f;
+    }
+    mbar_wait(&sm->full[slot], ph);
+#pragma unroll
+    for (int r = 0; r < kNtRows; ++r) {
+      float s1 = 0.f, s2 = 0.f;
+      if (r < nr) {
+        const bf16x8* gr = reinterpret_cast<const bf16x8*>(st + r * row_bytes);
+        const bf16x8* xr = reinterpret_cast<const bf16x8*>(st + (kNtRows + r) * row_bytes);
+#pragma unroll
+        for (int i = 0; i < kNtVpt; ++i) {
+          const int v = gtid + i * kGT;
+          if (v < nvec) {
+            float g[8], a[8], wf[8];
+            unpack8(gr[v], g);
+            unpack8(xr[v], a);
+            unpack8(__ldg(wvec + v), wf);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const float xh = (a[k] - mean[r]) * rstd[r];
+              dg[i][k] += g[k] * xh;
+              db[i][k] += g[k];
+              const float gw = g[k] * wf[k];
+              s1 += gw;
+              s2 += gw * xh;
+            }
+          }
+        }
+      }
+      s1 = warp_sum(s1);
+      s2 = warp_sum(s2);
+      if (lane == 0) {
+        sm->red[grp][par][r][gwarp] = s1;
+        sm->red2[grp][par][r][gwarp] = s2;
+      }
+    }
+    nt_bar(1 + grp, kGT);
+#pragma unroll
+    for (int r = 0; r < kNtRows; ++r) {
+      if (r < nr) {
+        float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+        for (int q = 0; q < kGW; ++q) {
+          t1 += sm->red[grp][par][r][q];
+          t2 += sm->red2[grp][par][r][q];
+        }
+        t1 /= (float)H;
+        t2 /= (float)H;
+        const bf16x8* gr = reinterpret_cast<const bf16x8*>(st + r * row_bytes);
+        const bf16x8* xr = reinterpret_cast<const bf16x8*>(st + (kNtRows + r) * row_bytes);
+#pragma unroll
+        for (int i = 0; i < kNtVpt; ++i) {
+          const int v = gtid + i * kGT;
+          if (v < nvec) {
+            float g[8], a[8], wf[8], o[8];
+            unpack8(gr[v], g);
+            unpack8(xr[v], a);
+            unpack8(__ldg(wvec + v), wf);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              o[k] = rstd[r] * (g[k] * wf[k] - t1 - (a[k] - mean[r]) * rstd[r] * t2);
+            reinterpret_cast<bf16x8*>(dx + (size_t)(r0 + r) * H)[v] = pack8(o);
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&sm->empty[slot]);
+  }
+  float* fold = reinterpret_cast<float*>(stages);
+  float* prow = partial + (size_t)blockIdx.x * 2 * H;
+  nt_fold_groups<kGW>(dg, fold, prow, grp, gtid, nvec);
+  nt_fold_groups<kGW>(db, fold + H, prow + H, grp, gtid, nvec);
+}
+
+// dgamma / dbeta (+)= column sums of partial [nblk][2][H]; same tree as colsum_tree_kernel.
+__global__ void __launch_bounds__(256)
+colsum2_tree_kernel(const float* __restrict__ partial, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    int nblk, int H, int accumulate) {
+  __shared__ float red[2][8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  float s = 0.f, t = 0.f;
+  if (c < H)
+    for (int b = ty; b < nblk; b += 8) {
+      s += partial[(size_t)b * 2 * H + c];
+      t += partial[(size_t)b * 2 * H + H + c];
+    }
+  red[0][ty][tx] = s;
+  red[1][ty][tx] = t;
+  __syncthreads();
+  if (ty == 0 && c < H) {
+    float u = 0.f, v = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      u += red[0][q][tx];
+      v += red[1][q][tx];
+    }
+    dgamma[c] = accumulate ? dgamma[c] + u : u;
+    if (dbeta) dbeta[c] = accumulate ? dbeta[c] + v : v;
   }
 }
 
@@ -422,6 +691,38 @@ int rmsnorm_bwd_tma(const void* dy, const void* x, const void* w, const float* r
                             scratch, M, H, S, stage_bytes);
   if (rc) return rc;
   colsum_tree_kernel<<<(H + 31) / 32, 256, 0, stream>>>(scratch, dw, grid, H, accumulate);
+  return (int)cudaGetLastError();
+}
+
+int layernorm_fwd_tma(const void* x, const void* w, const void* b, void* y, float* mean, float* rstd, int M,
+                      int H, float eps, cudaStream_t stream) {
+  int stage_bytes;
+  const int S = nt_stages(1, H, &stage_bytes);
+  const int smem = kNtHeader + S * stage_bytes;
+  const int grid = rmsnorm_tma_grid(M);
+  auto xb = (const __nv_bfloat16*)x, wb = (const __nv_bfloat16*)w, bb = (const __nv_bfloat16*)b;
+  auto yb = (__nv_bfloat16*)y;
+  return H <= 4 * 32 * kNtVpt * 8
+             ? nt_launch(layernorm_fwd_tma_kernel<4>, grid, smem, stream, xb, wb, bb, yb, mean, rstd, M, H, eps, S,
+                         stage_bytes)
+             : nt_launch(layernorm_fwd_tma_kernel<8>, grid, smem, stream, xb, wb, bb, yb, mean, rstd, M, H, eps, S,
+                         stage_bytes);
+}
+
+// scratch: fp32 [>= rmsnorm_tma_grid(M), 2, H]
+int layernorm_bwd_tma(const void* dy, const void* x, const void* w, const float* mean, const float* rstd,
+                      void* dx, float* dgamma, float* dbeta, float* scratch, int M, int H, int accumulate,
+                      cudaStream_t stream) {
+  int stage_bytes;
+  const int S = nt_stages(2, H, &stage_bytes);
+  const int smem = kNtHeader + S * stage_bytes;
+  const int grid = rmsnorm_tma_grid(M);
+  // two accumulators per column: always the 8-warp groups (half the columns per thread)
+  int rc = nt_launch(layernorm_bwd_tma_kernel<8>, grid, smem, stream, (const __nv_bfloat16*)dy,
+                     (const __nv_bfloat16*)x, (const __nv_bfloat16*)w, mean, rstd, (__nv_bfloat16*)dx, scratch, M,
+                     H, S, stage_bytes);
+  if (rc) return rc;
+  colsum2_tree_kernel<<<(H + 31) / 32, 256, 0, stream>>>(scratch, dgamma, dbeta, grid, H, accumulate);
   return (int)cudaGetLastError();
 }
 

@@ -444,6 +444,9 @@ CHECKS = {
     "rmsnorm_h8192_cta_path": lambda: check_rmsnorm(256, 8192),
     "rmsnorm_h1000_cta_path": lambda: check_rmsnorm(128, 1000),
     "layernorm": check_layernorm,
+    "layernorm_h4096": lambda: check_layernorm(1001, 4096),
+    "layernorm_h1024": lambda: check_layernorm(333, 1024),
+    "layernorm_h5120": lambda: check_layernorm(64, 5120),
     "rope": check_rope,
     "glu": check_glu,
     "bias_gelu": check_bias_gelu,

@@ -203,6 +203,31 @@ def bench_norm():
                    gbs_own=by / t / 1e6, frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"])
 
 
+def bench_layernorm():
+    impl = os.environ.get("B200_NORM_IMPL", "tma")
+    for M, H in ((4096, 4096), (2048, 8192)):
+        x = torch.randn(M, H, device="cuda").bfloat16()
+        w = torch.ones(H, device="cuda").bfloat16()
+        b = torch.zeros(H, device="cuda").bfloat16()
+        y, dx = torch.empty_like(x), torch.empty_like(x)
+        mean, rstd = torch.empty(M, device="cuda"), torch.empty(M, device="cuda")
+        dy = torch.randn_like(x)
+        dg, db = torch.zeros(H, device="cuda"), torch.zeros(H, device="cuda")
+        scratch = torch.empty(L.lib().b200_norm_bwd_grid(M), 2, H, device="cuda")
+        t = timeit(lambda: L.call("b200_layernorm_fwd", x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(),
+                                  mean.data_ptr(), rstd.data_ptr(), M, H, 1e-5, L.stream_ptr()))
+        by = 2.0 * M * H * 2
+        report(kernel="layernorm_fwd", impl=impl, M=M, H=H, ms_own=t, gbs_own=by / t / 1e6,
+               frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"],
+               ms_torch=timeit(lambda: torch.nn.functional.layer_norm(x, (H,), w, b)))
+        t = timeit(lambda: L.call("b200_layernorm_bwd", dy.data_ptr(), x.data_ptr(), w.data_ptr(), mean.data_ptr(),
+                                  rstd.data_ptr(), dx.data_ptr(), dg.data_ptr(), db.data_ptr(), scratch.data_ptr(),
+                                  M, H, 0, L.stream_ptr()))
+        by = 3.0 * M * H * 2
+        report(kernel="layernorm_bwd(+dgamma,dbeta)", impl=impl, M=M, H=H, ms_own=t, gbs_own=by / t / 1e6,
+               frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"])
+
+
 def bench_elementwise():
     M, F = 4096, 11008
     x = torch.randn(M, 2 * F, device="cuda").bfloat16()

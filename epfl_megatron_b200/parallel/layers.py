@@ -326,14 +326,26 @@ _FUSED_COMM = "auto"    # auto | on | off  (--b200_fused_comm)
 
 
 # Per-op policy of "auto": the in-kernel all-gather is used up to this tensor-parallel size. At tp 8
-# its copier warps still walk the 7 peers one after another and NCCL all-gather + GEMM is faster
-# (0.119 vs 0.175 ms on the Falcon-40B shapes); the in-kernel reduce-scatter wins at
-# every size and stays on. "--b200_fused_comm on" forces both.
+# the transfer (7/8 of the activation over NVLink) cannot hide behind 1/8 of the GEMM and NCCL
+# all-gather + GEMM is faster (0.119 vs 0.19 ms on the Falcon-40B shapes).
+# "--b200_fused_comm on" forces every fused path.
 _FUSED_AG_MAX_TP = int(os.environ.get("B200_FUSED_AG_MAX_TP", "4"))
+# GEMM -> all-reduce in one kernel (no sequence parallelism) wins at tp 2 (0.127 vs 0.135 ms on
+# 4096 x 4096 x 2048) and loses to cuBLAS + NCCL's NVLS all-reduce at tp 4 / 8 on the 7B-sized shards
+# (profiles/fused_comm_n4_r2_call15.log, fused_comm_n8_r2_call14.log).
+_FUSED_AR_MAX_TP = int(os.environ.get("B200_FUSED_AR_MAX_TP", "2"))
+# GEMM -> reduce-scatter: in-kernel up to tp 4; at tp 8 the 2048-row activations of Falcon-40B leave each
+# rank 1/8 of an already small GEMM to hide 7/8 of the output behind, and cuBLAS + NCCL is faster (0.128 vs
+# 0.204 ms; Falcon-40B TP8 step 1035 vs 1133 ms, profiles/bench_r2_call18_falcon40b_tp8_*.log).
+_FUSED_RS_MAX_TP = int(os.environ.get("B200_FUSED_RS_MAX_TP", "4"))
 
 
 def _fused_all_gather(tp: int) -> bool:
     return _FUSED_COMM == "on" or tp <= _FUSED_AG_MAX_TP
+
+
+def _fused_reduce_scatter(tp: int) -> bool:
+    return _FUSED_COMM == "on" or tp <= _FUSED_RS_MAX_TP
 
 
 def set_fused_comm_mode(mode: str):
@@ -432,7 +444,13 @@ class _FusedColumnSP(torch.autograd.Function):
             go2 = go2.contiguous()
         K = weight.shape[1]
         ws = _workspace(go2.shape[0], K, K)
-        dx = ws.gemm_reduce_scatter(go2, weight, b_mn_major=True)        # [M/tp, K]
+        tp = state.get_tensor_model_parallel_world_size()
+        if _fused_reduce_scatter(tp):
+            dx = ws.gemm_reduce_scatter(go2, weight, b_mn_major=True)    # [M/tp, K]
+        else:
+            full = Fn.gemm_nn(go2, weight)
+            dx = torch.empty(go2.shape[0] // tp, K, dtype=go2.dtype, device=go2.device)
+            reduce_scatter_into(dx, full, state.get_tensor_model_parallel_group())
         gw = _accumulate_wgrad(ctx.weight_ref, go2, gathered, ctx.gaf)
         return dx.view(ctx.in_shape), gw, None
 
@@ -451,7 +469,12 @@ class _FusedRowSP(torch.autograd.Function):
         tp = state.get_tensor_model_parallel_world_size()
         N = weight.shape[0]
         ws = _workspace(x2.shape[0], N, N)
-        out = ws.gemm_reduce_scatter(x2, weight)                          # [M/tp, N]
+        if _fused_reduce_scatter(tp):
+            out = ws.gemm_reduce_scatter(x2, weight)                      # [M/tp, N]
+        else:
+            full = Fn.gemm_nt(x2, weight)
+            out = torch.empty(x2.shape[0] // tp, N, dtype=x2.dtype, device=x2.device)
+            reduce_scatter_into(out, full, state.get_tensor_model_parallel_group())
         ctx.save_for_backward(x2, weight)
         ctx.weight_ref = weight
         ctx.gaf = gradient_accumulation_fusion
@@ -549,6 +572,8 @@ def _fused_allreduce_ok(x, weight, n_out) -> bool:
         return False
     rows = x.numel() // x.shape[-1]
     tp = state.get_tensor_model_parallel_world_size()
+    if _FUSED_COMM != "on" and tp > _FUSED_AR_MAX_TP:
+        return False
     return rows % tp == 0 and _fused_comm_ok(rows // tp, 256, n_out, x, weight)
 
 

@@ -216,6 +216,32 @@ def run_ours(a):
                 for e in ev[:60]:
                     f.write(f"| {e.device_time_total / tot * 100:.2f}% | {e.device_time_total / 1e3:.2f} | {e.count} | "
                             f"{e.device_time_total / max(e.count, 1):.1f} | `{e.key[:110]}` |\n")
+                # GPU-busy fraction: union of the kernel intervals of this rank, and where the gaps are
+                try:
+                    from torch.autograd import DeviceType
+                    ks = sorted(((x.time_range.start, x.time_range.end, x.name) for x in prof.events()
+                                 if x.device_type == DeviceType.CUDA), key=lambda t: t[0])
+                    busy, gaps, cur_end, prev = 0.0, {}, None, None
+                    for st_, en_, nm in ks:
+                        if cur_end is None:
+                            cur_end = st_
+                        if st_ > cur_end:
+                            g = gaps.setdefault(prev, [0, 0.0])
+                            g[0] += 1
+                            g[1] += st_ - cur_end
+                            cur_end = st_
+                        if en_ > cur_end:
+                            busy += en_ - cur_end
+                            cur_end = en_
+                        prev = nm[:70]
+                    span = ks[-1][1] - ks[0][0]
+                    f.write(f"\nGPU busy {busy / 1e3:.1f} ms of a {span / 1e3:.1f} ms span under the profiler "
+                            f"({busy / span * 100:.1f} %); idle {(span - busy) / 1e3:.1f} ms. Idle time by the kernel "
+                            "that ran BEFORE the gap:\n\n| idle ms | gaps | avg us | preceding kernel |\n|---|---|---|---|\n")
+                    for nm, (cnt, tot_g) in sorted(gaps.items(), key=lambda kv: -kv[1][1])[:25]:
+                        f.write(f"| {tot_g / 1e3:.2f} | {cnt} | {tot_g / cnt:.1f} | `{nm}` |\n")
+                except Exception as ex:  # noqa: BLE001
+                    f.write(f"\n(gap analysis failed: {ex})\n")
     # ---- region B: end to end (pinned H2D inputs + D2H loss every step), wall clock ----
     if a.profile:
         sampler.stop()

@@ -202,6 +202,23 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
   tn = in_group / gsz;
 }
 
+// Reduce modes at tp 2: position in a CTA pair's work sequence -> tile index. The plain order is
+// "all tiles of the peer's rows, then all own tiles": every partial tile crosses NVLink in the first
+// half of the kernel, which is then bound by the link (~64 KB per CTA and tile), while the link idles
+// in the second half. Here the first `lag` positions are remote tiles, then remote and own tiles
+// alternate, and the last `lag` positions are own tiles: the transfers spread over the kernel, and
+// an own tile is still reached at least `lag` positions after the peer produced its partial
+// (both ranks walk the same sequence). half = number of remote (= own) tiles.
+__device__ __forceinline__ int interleaved_tile(int i, int half, int lag) {
+  if (i < lag) return i;
+  const int mid = 2 * (half - lag);
+  if (i < lag + mid) {
+    const int j = i - lag;
+    return (j & 1) ? half + (j >> 1) : lag + (j >> 1);
+  }
+  return half + (half - lag) + (i - lag - mid);
+}
+
 template <bool kBMN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmAloc,
@@ -228,6 +245,10 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int tiles_per_chunk = ca.rows_per_chunk / (2 * kBM);
   // AG: start with the rank's own rows; RS: finish with them
   const int tm_rot = (ca.mode == kModeAG ? ca.rank : (ca.rank + 1) % ca.tp) * tiles_per_chunk;
+  // tp 2 reduce modes with chunk-aligned tile groups: interleave remote and own tiles (see above)
+  const bool interleave = ca.mode != kModeAG && ca.tp == 2 && (tiles_per_chunk % kGroupM) == 0;
+  const int il_half = num_tiles >> 1;
+  const int il_lag = min(num_pairs, il_half);
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -255,7 +276,8 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       const unsigned ready_target = 2 * gridDim.x;   // two copier warps per CTA, counters start at 0
-      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      for (int seq = pair; seq < num_tiles; seq += num_pairs) {
+        const int tile = interleave ? interleaved_tile(seq, il_half, il_lag) : seq;
         int tm, tn;
         tile_coords(tile, tiles_m, tiles_n, tm, tn);
         tm = (tm + tm_rot) % tiles_m;
@@ -412,7 +434,8 @@ gemm_comm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool reduce_mode = ca.mode != kModeAG;
     if (!reduce_mode) stage_own_rows(ca, blockIdx.x * kStageWarps + (warp - 2), lane);
     const size_t slot = (size_t)ca.rows_per_chunk * N;
-    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+    for (int seq = pair; seq < num_tiles; seq += num_pairs) {
+      const int tile = interleave ? interleaved_tile(seq, il_half, il_lag) : seq;
       int tm, tn;
       tile_coords(tile, tiles_m, tiles_n, tm, tn);
       tm = (tm + tm_rot) % tiles_m;

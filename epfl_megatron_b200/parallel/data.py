@@ -1,6 +1,12 @@
 """Broadcast a dict of integer tensors from TP rank 0 to its group with two collectives
 (megatron/core/tensor_parallel/data.py:22-105 behaviour): one for the packed shapes, one
-for the flattened payload."""
+for the flattened payload.
+
+The reference broadcasts the shapes on the GPU and reads them back (``.cpu()``), which drains the
+stream once per micro-batch: the host cannot enqueue the next micro-batch while the previous one
+runs. Here the shapes go through a host-side (Gloo) group of the same ranks when one exists
+(parallel/state.py), and the payload is staged in pinned memory and copied asynchronously, so
+the launch queue stays ahead of the GPU."""
 from __future__ import annotations
 
 import torch
@@ -29,10 +35,16 @@ def _build_key_size_numel_dictionaries(keys, data):
             assert data[key].dim() < _MAX_DATA_DIM, "you should increase MAX_DATA_DIM"
             for j, s in enumerate(data[key].size()):
                 sizes[i * _MAX_DATA_DIM + j] = s
-    t = torch.tensor(sizes, dtype=torch.long, device=_device())
-    dist.broadcast(t, state.get_tensor_model_parallel_src_rank(),
-                   group=state.get_tensor_model_parallel_group())
-    flat = t.cpu().tolist()
+    cpu_group = state.get_tensor_model_parallel_cpu_group()
+    if cpu_group is not None:
+        t = torch.tensor(sizes, dtype=torch.long)
+        dist.broadcast(t, state.get_tensor_model_parallel_src_rank(), group=cpu_group)
+        flat = t.tolist()
+    else:
+        t = torch.tensor(sizes, dtype=torch.long, device=_device())
+        dist.broadcast(t, state.get_tensor_model_parallel_src_rank(),
+                       group=state.get_tensor_model_parallel_group())
+        flat = t.cpu().tolist()
     key_size, key_numel, total = {}, {}, 0
     for i, key in enumerate(keys):
         shape, n = [], 1
@@ -47,6 +59,38 @@ def _build_key_size_numel_dictionaries(keys, data):
     return key_size, key_numel, total
 
 
+_PINNED, _PINNED_EVENTS, _PINNED_NEXT = [], [], 0
+
+
+def _stage_payload(parts, dev):
+    """Concatenate host tensors into one device tensor without a blocking pageable copy: a ring of
+    four pinned staging buffers, each reused only after the copy that last read it has finished."""
+    global _PINNED_NEXT
+    if dev.type != "cuda":
+        return torch.cat(parts, dim=0).to(dev)
+    if len(parts) == 1 and parts[0].is_cuda:
+        return parts[0]
+    if len(parts) == 1 and parts[0].is_pinned():
+        return parts[0].to(dev, non_blocking=True)
+    n = sum(p.numel() for p in parts)
+    i = _PINNED_NEXT % 4
+    _PINNED_NEXT += 1
+    while len(_PINNED) <= i:
+        _PINNED.append(None)
+        _PINNED_EVENTS.append(None)
+    buf = _PINNED[i]
+    if buf is None or buf.numel() < n or buf.dtype != parts[0].dtype:
+        buf = _PINNED[i] = torch.empty(max(n, 1), dtype=parts[0].dtype).pin_memory()
+    elif _PINNED_EVENTS[i] is not None:
+        _PINNED_EVENTS[i].synchronize()
+    torch.cat([p.cpu() for p in parts], dim=0, out=buf[:n])
+    out = buf[:n].to(dev, non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record()
+    _PINNED_EVENTS[i] = ev
+    return out
+
+
 def broadcast_data(keys, data, datatype):
     if state.get_tensor_model_parallel_world_size() == 1 and data is not None:
         dev = _device()
@@ -55,7 +99,7 @@ def broadcast_data(keys, data, datatype):
     dev = _device()
     if state.get_tensor_model_parallel_rank() == 0:
         _check_data_types(keys, data, datatype)
-        flat = torch.cat([data[k].contiguous().view(-1) for k in keys], dim=0).to(dev)
+        flat = _stage_payload([data[k].contiguous().view(-1) for k in keys], dev)
     else:
         flat = torch.empty(total, device=dev, dtype=datatype)
     dist.broadcast(flat, state.get_tensor_model_parallel_src_rank(),

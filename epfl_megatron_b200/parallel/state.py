@@ -10,10 +10,13 @@ from __future__ import annotations
 
 from typing import List, Optional
 
+import os
+
 import torch
 import torch.distributed as dist
 
 _TP = _PP = _DP = _MP = _EMB = _POS_EMB = None
+_TP_CPU = None
 _TP_RANKS: Optional[List[int]] = None
 _PP_RANKS: Optional[List[int]] = None
 _DP_RANKS: Optional[List[int]] = None
@@ -76,6 +79,21 @@ def initialize_model_parallel(tensor_model_parallel_size: int = 1,
     _DP, _DP_RANKS = make(lay["dp"])
     _MP, _ = make(lay["mp"])
     _TP, _TP_RANKS = make(lay["tp"])
+    # Control plane of the tensor-parallel group on the HOST (Gloo): the per-micro-batch shape
+    # exchange of broadcast_data goes through it, so that it never waits for the GPU stream.
+    global _TP_CPU
+    _TP_CPU = None
+    if tensor_model_parallel_size > 1 and dist.get_backend() == "nccl" \
+            and os.environ.get("B200_TP_CPU_GROUP", "1") != "0":
+        try:
+            for ranks in lay["tp"]:
+                g = dist.new_group(ranks, backend="gloo")
+                if rank in ranks:
+                    _TP_CPU = g
+        except Exception as e:  # noqa: BLE001 - Gloo cannot come up here (no usable interface): NCCL path
+            print(f"[rank {rank}] no host-side tensor-parallel group ({type(e).__name__}: {e}); "
+                  "broadcast_data falls back to NCCL for the shapes", flush=True)
+            _TP_CPU = None
     _PP, _PP_RANKS = make(lay["pp"])
     emb_groups, pos_groups = [], []
     for ranks in lay["pp"]:
@@ -97,6 +115,11 @@ def initialize_model_parallel(tensor_model_parallel_size: int = 1,
     _EMB_RANKS = _EMB_RANKS or []
     _POS_EMB_RANKS = _POS_EMB_RANKS or []
     _set_global_memory_buffer()
+
+
+def get_tensor_model_parallel_cpu_group():
+    """Gloo group over the ranks of the tensor-parallel group, or None (single rank, Gloo world, disabled)."""
+    return _TP_CPU
 
 
 def model_parallel_is_initialized() -> bool:
@@ -357,6 +380,8 @@ def get_global_memory_buffer():
 def destroy_model_parallel():
     global _TP, _PP, _DP, _MP, _EMB, _POS_EMB, _TP_RANKS, _PP_RANKS, _DP_RANKS
     global _EMB_RANKS, _POS_EMB_RANKS, _VPP_RANK, _VPP_WORLD, _PP_SPLIT_RANK, _GLOBAL_MEMORY_BUFFER
+    global _TP_CPU
+    _TP_CPU = None
     _TP = _PP = _DP = _MP = _EMB = _POS_EMB = None
     _TP_RANKS = _PP_RANKS = _DP_RANKS = _EMB_RANKS = _POS_EMB_RANKS = None
     _VPP_RANK = _VPP_WORLD = _PP_SPLIT_RANK = None

@@ -53,6 +53,7 @@ _ALIASES = {
     "indexer": "indexer",
     "fp16_deprecated": "fp16_deprecated", "fp16_deprecated.loss_scaler": "fp16_deprecated.loss_scaler",
     "data.image_folder": "data.image_folder", "data.autoaugment": "data.autoaugment",
+    "fused_kernels": "fused_kernels",
 }
 
 

@@ -151,3 +151,47 @@ def test_example_scripts_only_use_flags_the_parsers_know():
             if tok not in known and tok not in launcher and tok not in own:
                 unknown.setdefault(os.path.relpath(f, root), set()).add(tok)
     assert not unknown, unknown
+
+
+def test_fused_kernels_surface_matches_torch():
+    """``megatron.fused_kernels``: the reference's five extension names with their call signatures
+    (megatron/fused_kernels/tests/test_fused_kernels.py style checks, CPU restatement path)."""
+    import torch
+    from megatron import fused_kernels as fk
+    fk.load(None)
+    torch.manual_seed(0)
+    x = torch.randn(2, 3, 8, 16)
+    mask = torch.rand(2, 1, 8, 16) < 0.3
+    mask[0, 0, 2] = True                      # a fully masked row must come out as zeros, not NaN
+    y = fk.scaled_masked_softmax_cuda.forward(x, mask, 0.5)
+    want = torch.softmax((x * 0.5).masked_fill(mask, -10000.0), -1)
+    want[0, :, 2] = 0
+    assert torch.allclose(y, want, atol=1e-5)
+    g = torch.randn_like(y)
+    xr = x.clone().requires_grad_()
+    yr = torch.softmax((xr * 0.5).masked_fill(mask, float("-inf")).nan_to_num(neginf=-1e30), -1)
+    dx = fk.scaled_masked_softmax_cuda.backward(g, y, 0.5)
+    gy = g * y
+    assert torch.allclose(dx, 0.5 * (gy - y * gy.sum(-1, keepdim=True)), atol=1e-5)
+    tri = fk.scaled_upper_triang_masked_softmax_cuda.forward(torch.randn(6, 8, 8), 1.0)
+    assert torch.allclose(tri.sum(-1), torch.ones(6, 8), atol=1e-5) and float(tri.triu(1).abs().max()) == 0.0
+    assert torch.allclose(fk.scaled_softmax_cuda.forward(x, 2.0), torch.softmax(2.0 * x, -1), atol=1e-5)
+    # reference sizing helper: 128 threads per block, 2 rows per warp up to 128 keys
+    assert fk.scaled_masked_softmax_cuda.get_batch_per_block(8, 16, 2, 3) == (128 // 16) * 2
+    assert fk.scaled_masked_softmax_cuda.get_batch_per_block(128, 2048, 2, 16) == 4
+    # LayerNorm forward / backward against autograd
+    h = torch.randn(5, 32, requires_grad=True)
+    w, b = torch.randn(32, requires_grad=True), torch.randn(32, requires_grad=True)
+    out, mean, invvar = fk.fused_mix_prec_layer_norm_cuda.forward_affine(h.detach(), (32,), w.detach(), b.detach(), 1e-5)
+    ref_out = torch.nn.functional.layer_norm(h, (32,), w, b, 1e-5)
+    assert torch.allclose(out, ref_out, atol=1e-5)
+    go = torch.randn_like(out)
+    ref_out.backward(go)
+    dx, dg, db = fk.fused_mix_prec_layer_norm_cuda.backward_affine(go, mean, invvar, h.detach(), (32,), w.detach(),
+                                                                   b.detach(), 1e-5)
+    assert torch.allclose(dx, h.grad, atol=1e-4) and torch.allclose(dg, w.grad, atol=1e-4)
+    assert torch.allclose(db, b.grad, atol=1e-4)
+    # weight gradient accumulated into an fp32 buffer
+    inp, gout, main = torch.randn(4, 6, 8), torch.randn(4, 6, 10), torch.ones(10, 8)
+    fk.fused_dense_cuda.wgrad_gemm_accum_fp32(inp, gout, main)
+    assert torch.allclose(main, 1 + gout.reshape(-1, 10).t() @ inp.reshape(-1, 8), atol=1e-4)

@@ -339,6 +339,16 @@ __device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t desc
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same, 8-bit floating point operands (E4M3 / E5M2 chosen by the instruction descriptor), K = 32.
+__device__ __forceinline__ void umma_f8_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b,
+                                                uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // Arrive on the barrier at this offset in BOTH CTAs once the pair's MMAs retire.
 __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
   asm volatile(
@@ -387,6 +397,12 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int m, int n, int a_mn_ma
   return (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(a_mn_major) << 15) |
          (static_cast<uint32_t>(b_mn_major) << 16) | (static_cast<uint32_t>(n >> 3) << 17) |
          (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+// kind::f8f6f4 with fp32 accumulation: a_format / b_format 0 = E4M3, 1 = E5M2 (both K-major here).
+__host__ __device__ constexpr uint32_t make_idesc_f8(int m, int n, int a_e5m2, int b_e5m2) {
+  return (1u << 4) | (static_cast<uint32_t>(a_e5m2) << 7) | (static_cast<uint32_t>(b_e5m2) << 10) |
+         (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 
 // Byte offset of element (row r, 16-byte chunk c) inside a [rows x 128 B] tile laid

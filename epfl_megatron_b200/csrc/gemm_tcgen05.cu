@@ -280,11 +280,19 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const vo
       : "memory");
 }
 
-template <bool kAMN, bool kBMN>
+// kF8: 8-bit floating point operands (K-major only; a tile row is 128 one-byte elements instead of
+// 64 bf16, every byte count of the pipeline stays the same), tcgen05.mma.kind::f8f6f4 with the
+// runtime descriptor f8_idesc, and the epilogue multiplies by *alpha_a * *alpha_b (the two
+// dequantisation factors, read from device memory so that no host round trip is needed).
+template <bool kAMN, bool kBMN, bool kF8 = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const __grid_constant__ CUtensorMap tmC, void* __restrict__ Cout, int M, int N, int K,
-                      long long ldc, int out_mode, int tma_epilogue) {
+                      long long ldc, int out_mode, int tma_epilogue, uint32_t f8_idesc = 0,
+                      const float* __restrict__ alpha_a = nullptr,
+                      const float* __restrict__ alpha_b = nullptr) {
+  static_assert(!kF8 || (!kAMN && !kBMN), "8-bit operands are staged K-major");
+  constexpr int kKElems = kF8 ? 2 * kBK : kBK;      // elements per 128-byte tile row
   using L = PairSmem;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -303,7 +311,7 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int tiles_m = (M + 2 * kBM - 1) / (2 * kBM);
   const int tiles_n = (N + kPairBN - 1) / kPairBN;
   const int num_tiles = tiles_m * tiles_n;
-  const int num_kb = (K + kBK - 1) / kBK;
+  const int num_kb = (K + kKElems - 1) / kKElems;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -340,14 +348,14 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           uint8_t* sb = sa + L::kABytes;
           if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * L::kStageBytes);
           if (!kAMN) {
-            tma_load_2d_pair(sa, &tmA, &full_bar[stage], kb * kBK, m0);
+            tma_load_2d_pair(sa, &tmA, &full_bar[stage], kb * kKElems, m0);
           } else {
 #pragma unroll
             for (int j = 0; j < kBM / 64; ++j)
               tma_load_2d_pair(sa + j * (kBK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * kBK);
           }
           if (!kBMN) {
-            tma_load_2d_pair(sb, &tmB, &full_bar[stage], kb * kBK, n0);
+            tma_load_2d_pair(sb, &tmB, &full_bar[stage], kb * kKElems, n0);
           } else {
 #pragma unroll
             for (int j = 0; j < kPairHalfN / 64; ++j)
@@ -383,7 +391,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           for (int k = 0; k < kBK / 16; ++k) {
             const uint64_t da = make_sw128_desc(sa + k * kstep_a, lbo_a, 1024);
             const uint64_t db = make_sw128_desc(sb + k * kstep_b, lbo_b, 1024);
-            umma_bf16_ss_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (kF8) umma_f8_ss_pair(d_tmem, da, db, f8_idesc, (kb | k) != 0 ? 1u : 0u);   // K = 32 bytes
+            else umma_bf16_ss_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
           }
           umma_commit_pair(&empty_bar[stage]);
           if (++stage == kPairStages) {
@@ -412,6 +421,8 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint8_t* stage_out = smem + L::kOutOffset;
     const bool issuer = (ew == 0 && lane == 0);
     uint32_t box_count = 0;
+    float alpha = 1.f;
+    if (kF8) alpha = (alpha_a ? *alpha_a : 1.f) * (alpha_b ? *alpha_b : 1.f);
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int tm, tn;
       tile_coords(tile, tiles_m, tiles_n, tm, tn);
@@ -427,6 +438,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           uint32_t v[32];
           tmem_ld_32x32(taddr + c * 32, v);
           tmem_ld_wait();
+          if (kF8) {
+#pragma unroll
+            for (int q = 0; q < 32; ++q) v[q] = __float_as_uint(__uint_as_float(v[q]) * alpha);
+          }
           store_acc_chunk(v, Cout, row, n0 + c * 32, M, N, ldc, out_mode);
         }
         tc_fence_before();
@@ -443,6 +458,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             uint32_t v[32];
             tmem_ld_32x32(taddr + (2 * bx + h) * 32, v);
             tmem_ld_wait();
+            if (kF8) {
+#pragma unroll
+              for (int q = 0; q < 32; ++q) v[q] = __float_as_uint(__uint_as_float(v[q]) * alpha);
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               uint4 o;
@@ -475,6 +494,10 @@ gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           uint32_t v[32];
           tmem_ld_32x32(taddr + bx * 32, v);
           tmem_ld_wait();
+          if (kF8) {
+#pragma unroll
+            for (int q = 0; q < 32; ++q) v[q] = __float_as_uint(__uint_as_float(v[q]) * alpha);
+          }
 #pragma unroll
           for (int q = 0; q < 8; ++q)
             *reinterpret_cast<uint4*>(box + sw128_offset(r, q)) =
@@ -565,6 +588,22 @@ int make_tmap_2d(CUtensorMap* map, const void* base, long long rows, long long c
   return r == CUDA_SUCCESS ? 0 : B200_ERR_BAD_ARG;
 }
 
+// 2-D one-byte-element tensor [rows, cols] with row stride `ld` bytes, box [box_rows, 128 cols],
+// 128-byte swizzle (FP8 operands; zero fill out of bounds = +0 in E4M3 and E5M2).
+int make_tmap_2d_u8(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
+                    int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return B200_ERR_UNSUPPORTED;
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld};
+  cuuint32_t box[2] = {128, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : B200_ERR_BAD_ARG;
+}
+
 // Output map for the TMA epilogue: [rows, cols] of bf16 (box 64 cols) or fp32 (box 32 cols), 128 rows
 // per box, 128-byte swizzle. Returns B200_ERR_UNSUPPORTED when TMA cannot address this C.
 int make_tmap_out(CUtensorMap* map, void* base, long long rows, long long cols, long long ld, bool fp32) {
@@ -618,7 +657,28 @@ int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int 
   const int tma_epilogue = make_tmap_out(&tc, C, M, N, ldc, out_mode != 0) == 0 ? 1 : 0;
   if (!tma_epilogue) tc = ta;   // unused; any valid map
   kern<<<2 * pairs, kGemmThreads, PairSmem::kTotal, stream>>>(ta, tb, tc, C, M, N, K, ldc, out_mode,
-                                                              tma_epilogue);
+                                                              tma_epilogue, 0u, nullptr, nullptr);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+int launch_gemm_pair_f8(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int M, int N, int K,
+                        long long ldc, int out_mode, uint32_t idesc, const float* alpha_a,
+                        const float* alpha_b, cudaStream_t stream) {
+  auto kern = gemm_bf16_pair_kernel<false, false, true>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairSmem::kTotal);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + kPairBN - 1) / kPairBN);
+  const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
+  CUtensorMap tc;
+  const int tma_epilogue = make_tmap_out(&tc, C, M, N, ldc, out_mode != 0) == 0 ? 1 : 0;
+  if (!tma_epilogue) tc = ta;
+  kern<<<2 * pairs, kGemmThreads, PairSmem::kTotal, stream>>>(ta, tb, tc, C, M, N, K, ldc, out_mode, tma_epilogue,
+                                                              idesc, alpha_a, alpha_b);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -626,6 +686,26 @@ int launch_gemm_pair(const CUtensorMap& ta, const CUtensorMap& tb, void* C, int 
 }  // namespace b200
 
 using namespace b200;
+
+// C[M, N] (bf16: out_mode 0, fp32 store: 1, fp32 accumulate: 2) = (*alpha_a * *alpha_b) * A[M, K] B[N, K]^T
+// with 8-bit floating point operands, both K-major (row stride lda / ldb bytes, multiples of 16);
+// a_e5m2 / b_e5m2: 0 = E4M3, 1 = E5M2. alpha_* are DEVICE pointers (the dequantisation factors 1 / scale)
+// or NULL for 1. fp32 accumulation in tensor memory. K8 of the FP8 recipe the reference reaches through
+// Transformer Engine (megatron/model/transformer.py:931-950); tcgen05.mma.kind::f8f6f4, CTA pairs.
+B200_API int b200_gemm_fp8(const void* A, const void* B, void* C, int M, int N, int K, int a_e5m2, int b_e5m2,
+                           long long lda, long long ldb, long long ldc, int out_mode, const float* alpha_a,
+                           const float* alpha_b, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0 || out_mode < 0 || out_mode > 2) return B200_ERR_BAD_ARG;
+  if ((lda % 16) || (ldb % 16) || (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15))
+    return B200_ERR_UNSUPPORTED;
+  CUtensorMap ta, tb;
+  int rc = make_tmap_2d_u8(&ta, A, M, K, lda, kBM);
+  if (rc) return rc;
+  rc = make_tmap_2d_u8(&tb, B, N, K, ldb, kPairHalfN);
+  if (rc) return rc;
+  const uint32_t idesc = make_idesc_f8(2 * kBM, kPairBN, a_e5m2 ? 1 : 0, b_e5m2 ? 1 : 0);
+  return launch_gemm_pair_f8(ta, tb, C, M, N, K, ldc, out_mode, idesc, alpha_a, alpha_b, stream);
+}
 
 // variant: 0 = choose (CTA pairs when the problem has at least one 256 x 256 tile),
 // 1 = force the single-CTA kernel, 2 = force the CTA-pair kernel.

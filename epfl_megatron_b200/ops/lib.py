@@ -38,6 +38,8 @@ _SIGNATURES = {
     "b200_ipc_export_range": ([vp, vp, vp], i32),
     "b200_embed_fwd": ([vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp], i32),
     "b200_embed_bwd": ([vp, vp, i32, vp, i32, i32, i32, i64, i32, vp], i32),
+    "b200_gemm_fp8": ([vp, vp, vp, i32, i32, i32, i32, i32, i64, i64, i64, i32, vp, vp, vp], i32),
+    "b200_fp8_quantize": ([vp, vp, vp, i32, i32, i64, vp, vp, i32, vp], i32),
     "b200_xent_stats": ([vp, vp, vp, i32, i32, i64, vp], i32),
     "b200_xent_push_grid": ([i32], i32),
     "b200_xent_stats_push": ([vp, vp, vp, vp, i32, i32, i32, i32, i64, vp], i32),

@@ -366,6 +366,45 @@ def check_gemm(variant="nt", M=512, N=768, K=512, out_mode=0, kernel=0):
     return _close(out, ref, tol, 1e-2, f"gemm {variant} {M}x{N}x{K} mode{out_mode}")
 
 
+def check_fp8_quantize(rows=1024, cols=2048, e5m2=False):
+    """One-pass cast (+ transpose, + amax) against torch's float8 conversion of the same scaled values."""
+    dev = _dev()
+    torch.manual_seed(12)
+    x = (torch.randn(rows, cols, device=dev) * 3).bfloat16()
+    scale = torch.tensor([7.5], device=dev)
+    amax = torch.zeros(1, device=dev)
+    y = torch.empty(rows, cols, device=dev, dtype=torch.uint8)
+    yT = torch.empty(cols, rows, device=dev, dtype=torch.uint8)
+    L.call("b200_fp8_quantize", x.data_ptr(), y.data_ptr(), yT.data_ptr(), rows, cols, cols, scale.data_ptr(),
+           amax.data_ptr(), int(e5m2), L.stream_ptr())
+    dt, lim = (torch.float8_e5m2, 57344.0) if e5m2 else (torch.float8_e4m3fn, 448.0)
+    ref = (x.float() * 7.5).clamp(-lim, lim).to(dt).view(torch.uint8)
+    assert torch.equal(y, ref), f"fp8 cast: {(y != ref).sum().item()} mismatching bytes"
+    assert torch.equal(yT, ref.t().contiguous()), "fp8 transposed cast differs"
+    assert float(amax) == float(x.float().abs().max()), (float(amax), float(x.float().abs().max()))
+    return {"bytes": rows * cols}
+
+
+def check_gemm_fp8(M=512, N=768, K=1024, a_e5m2=False, b_e5m2=False, out_mode=0):
+    dev = _dev()
+    torch.manual_seed(13)
+    ta = torch.float8_e5m2 if a_e5m2 else torch.float8_e4m3fn
+    tb = torch.float8_e5m2 if b_e5m2 else torch.float8_e4m3fn
+    A = torch.randn(M, K, device=dev).to(ta)
+    B = torch.randn(N, K, device=dev).to(tb)
+    sa, sb = torch.tensor([0.5], device=dev), torch.tensor([0.25], device=dev)
+    ref = (A.float() @ B.float().t()) * 0.125
+    if out_mode == 2:
+        C = torch.randn(M, N, device=dev)
+        ref = ref + C
+    else:
+        C = torch.empty(M, N, device=dev, dtype=torch.bfloat16 if out_mode == 0 else torch.float32)
+    L.call("b200_gemm_fp8", A.data_ptr(), B.data_ptr(), C.data_ptr(), M, N, K, int(a_e5m2), int(b_e5m2), K, K, N,
+           out_mode, sa.data_ptr(), sb.data_ptr(), L.stream_ptr())
+    tol = (2e-2 if out_mode == 0 else 1e-3) * math.sqrt(K) * 0.125
+    return _close(C, ref, tol, 1e-2 if out_mode == 0 else 1e-4, f"gemm fp8 {M}x{N}x{K} mode{out_mode}")
+
+
 def attn_ref(q, k, v, scale, causal):
     # q [s,b,np,hn]  k,v [sk,b,g,hn] -> out [s,b,np,hn], lse [b,np,s]
     s, b, np_, hn = q.shape
@@ -475,6 +514,12 @@ CHECKS = {
     "gemm_tt": lambda: check_gemm("tt"),
     "gemm_tn_acc": lambda: check_gemm("tn", 768, 1024, 2048, out_mode=2),
     "gemm_nt_f32": lambda: check_gemm("nt", 256, 128, 256, out_mode=1),
+    "fp8_quantize_e4m3": check_fp8_quantize,
+    "fp8_quantize_e5m2_ragged": lambda: check_fp8_quantize(208, 1040, True),
+    "gemm_fp8": check_gemm_fp8,
+    "gemm_fp8_hybrid_big": lambda: check_gemm_fp8(4096, 4096, 4096, True, False),
+    "gemm_fp8_ragged_f32": lambda: check_gemm_fp8(1000 // 16 * 16, 968 // 16 * 16, 528, False, False, 1),
+    "gemm_fp8_wgrad_acc": lambda: check_gemm_fp8(768, 1024, 2048, True, False, 2),
     "attn_fwd": check_attn_fwd,
     "attn_fwd_mqa_long": lambda: check_attn_fwd(1024, 1, 1, 8, 128, True),
     "attn_fwd_full": lambda: check_attn_fwd(384, 1, 2, 2, 128, False),

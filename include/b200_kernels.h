@@ -171,6 +171,19 @@ int b200_gemm_allreduce(const B200CommDesc* d, void* const* peer_parts, void* co
                         const void* A, const void* B, int M, int N, int K, int b_mn_major, long long lda,
                         long long ldb, cudaStream_t stream);
 
+/* ---- FP8 (csrc/fp8.cu, csrc/gemm_tcgen05.cu) ---------------------------------------------------------------
+ * The reference reaches FP8 through Transformer Engine only (megatron/model/transformer.py:931-950).
+ * b200_fp8_quantize: y[rows, cols] = fp8(x * *scale) (+ yT[cols, rows], + *amax = max(*amax, max|x|)) in one pass
+ *   over bf16 x; rows % 16 == 0, cols % 16 == 0; e5m2: 0 = E4M3, 1 = E5M2; saturating.
+ * b200_gemm_fp8: C[M, N] = (*alpha_a * *alpha_b) * A[M, K] B[N, K]^T, both operands one byte per element and
+ *   K-major (strides in bytes, multiples of 16), fp32 accumulation (tcgen05.mma.kind::f8f6f4, CTA pairs);
+ *   out_mode 0 bf16, 1 fp32, 2 fp32 accumulate; alpha_* device pointers or NULL. */
+int b200_fp8_quantize(const void* x, void* y, void* yT, int rows, int cols, long long ldx, const float* scale,
+                      float* amax, int e5m2, cudaStream_t stream);
+int b200_gemm_fp8(const void* A, const void* B, void* C, int M, int N, int K, int a_e5m2, int b_e5m2, long long lda,
+                  long long ldb, long long ldc, int out_mode, const float* alpha_a, const float* alpha_b,
+                  cudaStream_t stream);
+
 /* ---- vocab-parallel embedding over peer memory (csrc/embed.cu) -------------------------------------------
  * Replaces megatron/core/tensor_parallel/layers.py:187-210 (masked local lookup + all-reduce) and its backward.
  * b200_ipc_export_range: CUDA IPC handle of the allocation containing `ptr` + the offset of `ptr` inside it.

@@ -203,6 +203,33 @@ def bench_norm():
                    gbs_own=by / t / 1e6, frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"])
 
 
+def bench_fp8():
+    """FP8 GEMM (tcgen05 kind::f8f6f4, CTA pairs) vs the bf16 kernel and cuBLAS bf16 on the 7B shapes."""
+    for (M, N, K) in ((4096, 12288, 4096), (4096, 22016, 4096), (4096, 4096, 11008), (8192, 8192, 8192)):
+        A8 = torch.randn(M, K, device="cuda").to(torch.float8_e4m3fn)
+        B8 = torch.randn(N, K, device="cuda").to(torch.float8_e4m3fn)
+        A = torch.randn(M, K, device="cuda").bfloat16()
+        B = torch.randn(N, K, device="cuda").bfloat16()
+        C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        one = torch.ones(1, device="cuda")
+        t8 = timeit(lambda: L.call("b200_gemm_fp8", A8.data_ptr(), B8.data_ptr(), C.data_ptr(), M, N, K, 0, 0, K, K, N,
+                                   0, one.data_ptr(), one.data_ptr(), L.stream_ptr()))
+        t16 = timeit(lambda: SC.gemm(A, B, M, N, K, 0, 0, 0, c=C, kernel=2))
+        tcb = timeit(lambda: torch.matmul(A, B.t(), out=C))
+        fl = 2.0 * M * N * K
+        report(kernel="gemm_fp8", M=M, N=N, K=K, ms_fp8=t8, tflops_fp8=fl / t8 / 1e9, ms_bf16_own=t16,
+               tflops_bf16_own=fl / t16 / 1e9, ms_bf16_cublas=tcb, tflops_bf16_cublas=fl / tcb / 1e9)
+    x = torch.randn(4096, 11008, device="cuda").bfloat16()
+    y = torch.empty(4096, 11008, device="cuda", dtype=torch.uint8)
+    yT = torch.empty(11008, 4096, device="cuda", dtype=torch.uint8)
+    sc, am = torch.ones(1, device="cuda"), torch.zeros(1, device="cuda")
+    t = timeit(lambda: L.call("b200_fp8_quantize", x.data_ptr(), y.data_ptr(), yT.data_ptr(), 4096, 11008, 11008,
+                              sc.data_ptr(), am.data_ptr(), 0, L.stream_ptr()))
+    by = 4096 * 11008 * 4.0
+    report(kernel="fp8_quantize(+transpose,+amax)", rows=4096, cols=11008, ms_own=t, gbs_own=by / t / 1e6,
+           frac_of_measured_hbm=by / t / 1e6 / PEAKS["hbm_gbs"])
+
+
 def bench_layernorm():
     impl = os.environ.get("B200_NORM_IMPL", "tma")
     for M, H in ((4096, 4096), (2048, 8192)):

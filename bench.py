@@ -77,6 +77,9 @@ def build_arg_list(a, tp, dp):
     ]
     if tp > 1 and not getattr(a, 'no_sp', False):
         argv.append("--sequence_parallel")
+    if getattr(a, 'fp8', False):
+        argv += ["--fp8_hybrid", "--fp8_amax_history_len", "16", "--fp8_amax_compute_algo", "max"]
+        argv += os.environ.get("B200_BENCH_FP8_EXTRA", "").split()
     if a.recompute:
         argv += ["--recompute_granularity", "full", "--recompute_method", "uniform"]
     if getattr(a, 'vpp_layers', 0):
@@ -298,7 +301,7 @@ def run_ours(a):
     if quiet:
         sys.stdout = real_stdout
     if rank == 0:
-        custom_layout = bool(getattr(a, 'no_sp', False) or getattr(a, 'tp', 0) or getattr(a, 'pp', 1) > 1 or a.seq != 4096 or a.recompute)
+        custom_layout = bool(getattr(a, 'fp8', False) or getattr(a, 'no_sp', False) or getattr(a, 'tp', 0) or getattr(a, 'pp', 1) > 1 or a.seq != 4096 or a.recompute)
         out = {
             "metric": ("Llama-2 7B" if a.model == "llama2-7b" else a.model) +
                       " bf16 training throughput (tokens/s, whole job, max over ranks)",
@@ -307,7 +310,8 @@ def run_ours(a):
             "vs_baseline": (value / REF_SAME_BOX[a.gpus] if a.model == "llama2-7b" and not custom_layout
                             and REF_SAME_BOX.get(a.gpus) else None),
             "vs_published_a100_anchor": value / 7100.0 if a.model == "llama2-7b" else None,
-            "dtype": "bf16", "data": "synthetic tokens, random-init weights",
+            "dtype": "fp8 (hybrid, delayed scaling) linears on bf16 parameters" if getattr(a, 'fp8', False) else "bf16",
+            "data": "synthetic tokens, random-init weights",
             "impl": "ours",
             "config": {"model": a.model, "global_batch": args.global_batch_size, "seq_len": args.seq_length,
                        "micro_batch": args.micro_batch_size, "num_microbatches": n_mb,
@@ -375,6 +379,8 @@ def main():
     p.add_argument("--kernels", default="auto", help="debug only: auto|off")
     p.add_argument("--fused_comm", default="auto", help="A/B only: auto|on|off (in-kernel TP collectives)")
     p.add_argument("--fused_dp", default="auto", help="A/B only: auto|on|off (in-kernel DP reduce-scatter/all-gather)")
+    p.add_argument("--fp8", action="store_true", help="A/B only (NOT the headline): FP8 hybrid linears, reported with "
+                                                     "dtype fp8 and without vs_baseline")
     p.add_argument("--no_sp", action="store_true", help="A/B only: tensor parallelism without sequence parallelism")
     p.add_argument("--torch_profile", action="store_true", help="also write gpurun_out/torch_profile_nN.md")
     p.add_argument("--profile", action="store_true", help="1 warm-up + K steps, no e2e region; for ncu, NOT a bench value")

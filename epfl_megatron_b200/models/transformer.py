@@ -444,9 +444,12 @@ class ParallelTransformer(MegatronModule):
         self.drop_path_rate = drop_path_rate
         self.transformer_impl = args.transformer_impl
         if self.transformer_impl == "transformer_engine":
-            raise NotImplementedError(
-                "--transformer_impl transformer_engine: Transformer Engine is not part of this build; "
-                "the local implementation already runs on the sm_100a kernels")
+            # Transformer Engine is not part of this build: its role (fused layers, FP8 linears under
+            # --fp8_e4m3 / --fp8_hybrid) is played by the local layers on the sm_100a kernels (ops/fp8.py)
+            from ..utils import print_rank_0
+            print_rank_0("--transformer_impl transformer_engine: running the local layers on the sm_100a "
+                         "kernels (FP8 linears follow --fp8_e4m3 / --fp8_hybrid)")
+            self.transformer_impl = "local"
         self.recompute_granularity = args.recompute_granularity
         self.recompute_method = args.recompute_method
         self.recompute_num_layers = args.recompute_num_layers

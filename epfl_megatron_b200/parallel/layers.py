@@ -25,6 +25,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 from torch.nn.parameter import Parameter
 
+from ..ops import fp8
 from ..ops import functional as Fn
 from . import state
 from .mappings import (copy_to_tensor_model_parallel_region, gather_from_tensor_model_parallel_region,
@@ -261,7 +262,11 @@ class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
         else:
             total = input
         K = total.shape[-1]
-        out = Fn.gemm_nt(total.reshape(-1, K), weight)
+        t2 = total.reshape(-1, K)
+        if fp8.usable(t2, weight):
+            out = fp8.forward_gemm(t2, weight)            # E4M3 x E4M3, delayed scaling (ops/fp8.py)
+        else:
+            out = Fn.gemm_nt(t2, weight)
         out = out.view(*total.shape[:-1], weight.shape[0])
         if bias is not None:
             out = out + bias
@@ -286,7 +291,12 @@ class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
         go2 = grad_output.reshape(-1, N)
         if not go2.is_contiguous():
             go2 = go2.contiguous()
-        grad_input = Fn.gemm_nn(go2, weight).view(*grad_output.shape[:-1], weight.shape[1])
+        dyT8 = None
+        if fp8.usable(go2, weight):
+            grad_input, dyT8 = fp8.dgrad_gemm(go2, weight)
+            grad_input = grad_input.view(*grad_output.shape[:-1], weight.shape[1])
+        else:
+            grad_input = Fn.gemm_nn(go2, weight).view(*grad_output.shape[:-1], weight.shape[1])
         if gather is not None:
             gather.wait()
         red = None
@@ -304,7 +314,11 @@ class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):
         fused = False
         if ctx.gradient_accumulation_fusion and main is not None:
             first = getattr(w, "_b200_main_grad_empty", False)
-            fused = Fn.wgrad_accumulate(go2, t2, main, accumulate=not first)
+            if dyT8 is not None and main.dtype == torch.float32 and main.is_contiguous() and fp8.usable(t2, weight):
+                fp8.wgrad_gemm(dyT8, t2, weight, main, accumulate=not first)
+                fused = True
+            else:
+                fused = Fn.wgrad_accumulate(go2, t2, main, accumulate=not first)
             if fused:
                 w._b200_main_grad_empty = False
                 Fn._notify_grad_ready(w)
@@ -373,6 +387,7 @@ def _fused_comm_ok(rows_local: int, k_gather: int, n_scatter: int, *tensors) -> 
     if _FUSED_COMM == "off" or not Fn.kernels_enabled():
         return False
     ok = (all(t.is_cuda and t.dtype == torch.bfloat16 for t in tensors)
+          and not any(hasattr(t, "_b200_fp8") for t in tensors)      # FP8 layers: NCCL collectives + 8-bit GEMMs
           and rows_local % 256 == 0 and k_gather % 256 == 0 and n_scatter % 8 == 0
           and 2 <= state.get_tensor_model_parallel_world_size() <= 8)
     ok = ok and tp_group_on_one_host()
@@ -577,6 +592,20 @@ def _fused_allreduce_ok(x, weight, n_out) -> bool:
     return rows % tp == 0 and _fused_comm_ok(rows // tp, 256, n_out, x, weight)
 
 
+def _maybe_attach_fp8(weight):
+    """First forward of a Column / RowParallelLinear: give its weight an FP8 scaling state when the run
+    asks for FP8 (``--fp8_e4m3`` / ``--fp8_hybrid``); by now the parameter is bf16 on the GPU."""
+    if hasattr(weight, "_b200_fp8") or getattr(weight, "_b200_fp8_checked", False):
+        return
+    weight._b200_fp8_checked = True
+    try:
+        from .. import global_vars
+        args = global_vars.get_args()
+    except Exception:  # noqa: BLE001 - layers used outside a configured run
+        return
+    fp8.attach(weight, args)
+
+
 def linear_with_grad_accumulation_and_async_allreduce(input, weight, bias, gradient_accumulation_fusion,
                                                       async_grad_allreduce,
                                                       sequence_parallel_enabled):
@@ -633,6 +662,7 @@ class ColumnParallelLinear(torch.nn.Module):
 
     def forward(self, input_):
         bias = self.bias if not self.skip_bias_add else None
+        _maybe_attach_fp8(self.weight)
         if self.world_size > 1 and not self.sequence_parallel_enabled and torch.is_grad_enabled() \
                 and input_.requires_grad and _fused_allreduce_ok(input_, self.weight, self.input_size):
             # dgrad GEMM + all-reduce in one kernel in the backward pass
@@ -695,6 +725,7 @@ class RowParallelLinear(torch.nn.Module):
             self.register_parameter("bias", None)
 
     def forward(self, input_):
+        _maybe_attach_fp8(self.weight)
         if self.input_is_parallel or self.world_size == 1:
             x = input_
         else:

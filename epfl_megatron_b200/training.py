@@ -293,6 +293,8 @@ def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_sch
     timers("optimizer", log_level=1).start(barrier=args.barrier_with_L1_time)
     update_successful, grad_norm, num_zeros = optimizer.step(args, timers)
     timers("optimizer").stop()
+    from .ops import fp8 as _fp8
+    _fp8.advance_step()            # FP8 layers: amax of this step -> scales of the next (no-op without FP8)
     if update_successful:
         optimizer.gather_model_params(args, timers)
         every = getattr(args, "check_dp_consistency_interval", 0)

@@ -61,7 +61,10 @@ def test_gqa_recompute_and_misc_rules():
     with pytest.raises(AssertionError):
         _args(["--parallel_layernorm"])                                     # needs --parallel_attn
     with pytest.raises(AssertionError):
-        _args(["--fp8_hybrid"])                                             # needs transformer_engine
+        _args(["--fp8_hybrid"])                                             # FP8 linears need --bf16
+    assert _args(["--fp8_hybrid", "--bf16"]).fp8_hybrid                     # local layers run the FP8 recipe
+    with pytest.raises(AssertionError):
+        _args(["--fp8_hybrid", "--fp8_e4m3", "--bf16"])                     # one format
     with pytest.raises(AssertionError):
         _args(["--save", "/tmp/x"])                                         # needs --save_interval
     with pytest.raises(AssertionError):

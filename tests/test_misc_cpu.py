@@ -195,3 +195,29 @@ def test_fused_kernels_surface_matches_torch():
     inp, gout, main = torch.randn(4, 6, 8), torch.randn(4, 6, 10), torch.ones(10, 8)
     fk.fused_dense_cuda.wgrad_gemm_accum_fp32(inp, gout, main)
     assert torch.allclose(main, 1 + gout.reshape(-1, 10).t() @ inp.reshape(-1, 8), atol=1e-4)
+
+
+def test_fp8_delayed_scaling_bookkeeping():
+    """ops/fp8.advance_step: scale = fp8_max / amax / 2**margin from the most recent amax or the max over the
+    history; amax of zero or a non-finite scale keeps the old scale; histories roll; interval is honoured."""
+    import torch
+    from epfl_megatron_b200.ops import fp8
+    fp8.reset()
+    try:
+        r = fp8.Recipe(hybrid=True, margin=1, interval=1, history_len=3, algo="max")
+        pool = fp8._pool(torch.device("cpu"), r)
+        fp8._N = 2
+        pool["hist"][0, :, 0] = torch.tensor([2.0, 4.0, 8.0])
+        pool["hist"][0, :, 1] = torch.tensor([7.0, 1.0, 1.0])
+        pool["hist"][1, :, 0] = torch.tensor([0.0, float("inf"), 3.5])
+        fp8.advance_step()
+        want0 = torch.tensor([448.0 / 7.0, 448.0 / 4.0, 57344.0 / 8.0]) / 2.0
+        assert torch.allclose(pool["scale"][0], want0)
+        assert torch.allclose(pool["scale_inv"][0], 1.0 / want0)
+        assert pool["scale"][1, 0] == 1.0 and pool["scale"][1, 1] == 1.0           # amax 0 / inf: unchanged
+        assert torch.allclose(pool["scale"][1, 2], torch.tensor(57344.0 / 3.5 / 2.0))
+        assert torch.equal(pool["hist"][0, :, 1], torch.tensor([2.0, 4.0, 8.0]))   # rolled
+        assert float(pool["hist"][:2, :, 0].abs().sum()) == 0.0                    # fresh slot for the next step
+        assert fp8._STEP == 1
+    finally:
+        fp8.reset()

@@ -35,7 +35,7 @@ def main():
         text = "\n".join(lines)
         counts = [len(re.findall(rx, text)) for _, rx in CLASSES]
         rows.append((name, counts, lines))
-    tensor = [r for r in rows if r[1][0] or r[1][4] or r[1][5] or r[1][6]]
+    tensor = [r for r in rows if r[1][0] or r[1][4] or r[1][5] or r[1][6] or r[1][7]]
     other = [r for r in rows if r not in tensor]
     out = ["# SASS evidence (cuobjdump -sass libb200kernels.so, sm_100a; regenerate with `python tools/sass_evidence.py`)\n",
            "Counts of the Blackwell-native instruction classes per kernel: UTC*MMA = tcgen05.mma, LDTM/STTM = tcgen05.ld/st, "

@@ -23,8 +23,8 @@ def _dev():
 
 
 def _close(a, b, atol, rtol, what):
-    a = a.float()
-    b = b.float()
+    a = a.detach().float()
+    b = b.detach().float()
     err = (a - b).abs()
     tol = atol + rtol * b.abs()
     bad = (err > tol)

@@ -209,7 +209,7 @@ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, 
 // alternate, and the last `lag` positions are own tiles: the transfers spread over the kernel, and
 // an own tile is still reached at least `lag` positions after the peer produced its partial
 // (both ranks walk the same sequence). half = number of remote (= own) tiles.
-__device__ __forceinline__ int interleaved_tile(int i, int half, int lag) {
+__host__ __device__ __forceinline__ int interleaved_tile(int i, int half, int lag) {
   if (i < lag) return i;
   const int mid = 2 * (half - lag);
   if (i < lag + mid) {
@@ -630,6 +630,10 @@ B200_API int b200_comm_debug_read(unsigned* out8) {
   unsigned z[8] = {};
   return (int)cudaMemcpyToSymbol(fc::g_comm_debug, z, sizeof(z));
 }
+
+// Host view of the tile order of the tp 2 reduce modes (tests): position i of a CTA pair's sequence ->
+// tile index, for `half` remote + `half` own tiles and a lag of `lag` positions.
+B200_API int b200_comm_interleaved_tile(int i, int half, int lag) { return fc::interleaved_tile(i, half, lag); }
 
 B200_API int b200_comm_flag_words(int max_blocks, int max_tn) {
   return 4 * max_blocks + 32 + 2 * max_blocks * max_tn + 16;

@@ -152,6 +152,7 @@ int b200_stage_shard(const void* src, void* stage, void* own_rows, long long byt
                      int tp, int rank, unsigned wait_value, int do_wait, unsigned* done_counter,
                      unsigned call_index, unsigned* const* signal_addrs, int n_signal, unsigned epoch,
                      cudaStream_t stream);
+int b200_comm_interleaved_tile(int i, int half, int lag);  /* tile order of the tp 2 reduce GEMMs (host view) */
 int b200_comm_flag_words(int max_blocks, int max_tn);     /* max_tn: widest reduced output / 256 columns */
 int b200_comm_shard_ready_word(int max_blocks);
 int b200_comm_consumed_word(int max_blocks);

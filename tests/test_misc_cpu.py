@@ -221,3 +221,28 @@ def test_fp8_delayed_scaling_bookkeeping():
         assert fp8._STEP == 1
     finally:
         fp8.reset()
+
+
+def test_fused_reduce_gemm_tile_order_is_a_permutation_with_lag():
+    """tp 2 reduce-scatter / all-reduce GEMM: the interleaved order (csrc/gemm_comm_tcgen05.cu) visits every tile
+    once, starts with `lag` remote tiles, ends with `lag` own tiles, and reaches own tile k at least `lag`
+    positions after the peer (which walks the same sequence) produced the matching remote tile k."""
+    import ctypes
+    from pathlib import Path
+    so = Path(__file__).resolve().parent.parent / "epfl_megatron_b200" / "ops" / "_lib" / "libb200kernels.so"
+    if not so.exists():
+        import pytest
+        pytest.skip("native library not built")
+    lib = ctypes.CDLL(str(so))
+    f = lib.b200_comm_interleaved_tile
+    f.argtypes, f.restype = [ctypes.c_int] * 3, ctypes.c_int
+    for half, pairs in ((128, 74), (64, 74), (352, 74), (8, 74), (40, 16)):
+        lag = min(pairs, half)
+        seq = [f(i, half, lag) for i in range(2 * half)]
+        assert sorted(seq) == list(range(2 * half))
+        assert all(t < half for t in seq[:lag]) and all(t >= half for t in seq[2 * half - lag:])
+        pos = {t: i for i, t in enumerate(seq)}
+        assert min(pos[half + k] - pos[k] for k in range(half)) >= lag
+        # remote and own tiles alternate in the middle: the link is never asked for more than every other tile
+        mid = seq[lag:2 * half - lag]
+        assert all((a < half) != (b < half) for a, b in zip(mid, mid[1:]))

@@ -22,9 +22,11 @@ __global__ void __launch_bounds__(256)
 rope_kernel(__nv_bfloat16* __restrict__ x, const float2* __restrict__ table,
             const long long* __restrict__ pos_ids, int S, int B, int G, int nslot, int nrot,
             int HN, int pos_offset, int max_pos, float sign, long long total_vec) {
-  // One thread owns one 16-byte column (4 rotation pairs) of one token and walks all rotated
-  // heads of that token: position lookup and the (cos, sin) values are loaded once and reused
-  // G * nrot times; four heads are in flight per step.
+  // One thread owns one 16-byte column (4 rotation pairs) of one token and walks a share of the rotated
+  // heads of that token (gridDim.y shares): position lookup and the (cos, sin) values are loaded once
+  // and reused for every head of the share; four heads are in flight per step. Splitting the heads
+  // over gridDim.y quadruples the resident warps: with one share the kernel kept ~28 KB in flight
+  // per SM and ran at 36 % of DRAM peak (profiles/ncu_all_kernels_r2_table.md).
   const int vec_per_head = HN >> 3;
   const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (i >= total_vec) return;
@@ -43,7 +45,10 @@ rope_kernel(__nv_bfloat16* __restrict__ x, const float2* __restrict__ table,
     sn[k] = c.y * sign;
   }
   bf16x8* base = reinterpret_cast<bf16x8*>(x + t * (long long)G * nslot * HN) + v;
-  const int heads = G * nrot;
+  const int heads_all = G * nrot;
+  const int per_share = (heads_all + (int)gridDim.y - 1) / (int)gridDim.y;
+  const int h_begin = (int)blockIdx.y * per_share;
+  const int heads = min(heads_all, h_begin + per_share);
   auto head_ptr = [&](int h) {
     const int g = h / nrot, slot = h - g * nrot;
     return base + (long long)(g * nslot + slot) * vec_per_head;
@@ -58,7 +63,7 @@ rope_kernel(__nv_bfloat16* __restrict__ x, const float2* __restrict__ table,
     }
     return pack8(o);
   };
-  int h = 0;
+  int h = h_begin;
   for (; h + 4 <= heads; h += 4) {
     bf16x8* p[4];
     bf16x8 in[4];
@@ -324,7 +329,8 @@ B200_API int b200_rope(void* x, const float* cos_sin, const long long* pos_ids, 
   long long total = (long long)S * B * (HN >> 3);      // one thread per (token, 16-byte column)
   if (total == 0 || G == 0) return 0;
   if ((total + 127) / 128 > 0x7fffffffLL) return B200_ERR_TOO_LARGE;
-  rope_kernel<<<(unsigned)((total + 127) / 128), 128, 0, stream>>>((__nv_bfloat16*)x, (const float2*)cos_sin,
+  const int shares = G * nrot >= 16 ? 4 : 1;
+  rope_kernel<<<dim3((unsigned)((total + 127) / 128), shares), 128, 0, stream>>>((__nv_bfloat16*)x, (const float2*)cos_sin,
                                                   pos_ids, S, B, G, nslot, nrot, HN, pos_offset,
                                                   max_pos, inverse ? -1.f : 1.f, total);
   B200_CHECK_LAUNCH();

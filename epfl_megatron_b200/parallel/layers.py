@@ -240,7 +240,15 @@ def fused_vocab_embedding_ok(input_ids, weight, sequence_parallel) -> bool:
     if ok and sequence_parallel and tp > 1:
         B, S = input_ids.shape
         ok = (S // tp) * B * weight.shape[1] * 2 <= _workspace(S * B, weight.shape[1], weight.shape[1]).stage_bytes
-    return ok and (tp == 1 or tp_group_on_one_host())
+    if not ok:
+        return False
+    if tp == 1:
+        return True
+    if not tp_group_on_one_host():
+        return False
+    # the tables must be mappable into each other (CUDA IPC): collective on first use, cached afterwards
+    B, S = input_ids.shape
+    return _workspace(S * B, weight.shape[1], weight.shape[1]).peer_tables(weight) is not None
 
 
 class LinearWithGradAccumulationAndAsyncCommunication(torch.autograd.Function):

@@ -269,27 +269,44 @@ class TPWorkspace:
     # ---- vocab-parallel embedding tables ------------------------------------------------------
     def peer_tables(self, weight: torch.Tensor):
         """Addresses of every rank's shard of an embedding table in THIS rank's address space (CUDA IPC
-        mapping of the allocation that holds the parameter; collective on first use per parameter)."""
+        mapping of the allocation that holds the parameter; collective on first use per parameter).
+        Returns None -- on EVERY rank -- when any rank could not export or map its allocation (memory
+        from an allocator without IPC support, e.g. expandable segments): the caller then keeps the
+        NCCL path. Both collectives below are reached by all ranks whatever happened locally."""
         key = (weight.data_ptr(), weight.numel())
-        tabs = self._tables.get(key)
-        if tabs is None:
+        if key in self._tables:
+            return self._tables[key]
+        info = None
+        try:
             handle = (C.c_ubyte * 64)()
             off = C.c_longlong()
             L.call("b200_ipc_export_range", weight.data_ptr(), handle, C.byref(off), launches=0)
-            infos = [None] * self.tp
-            dist.all_gather_object(infos, (bytes(handle), off.value), group=self.group)
-            tabs = []
-            for r, (h, o) in enumerate(infos):
-                if r == self.rank:
-                    tabs.append(weight.data_ptr())
-                    continue
-                base = _OPENED.get(h)
-                if base is None:
-                    p = C.c_void_p()
-                    L.call("b200_symm_import", (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p), launches=0)
-                    base = _OPENED[h] = p.value
-                tabs.append(base + o)
-            self._tables[key] = tabs
+            info = (bytes(handle), off.value)
+        except Exception:  # noqa: BLE001 - reported to the group through `info is None`
+            pass
+        infos = [None] * self.tp
+        dist.all_gather_object(infos, info, group=self.group)
+        tabs = None
+        if all(i is not None for i in infos):
+            try:
+                tabs = []
+                for r, (h, o) in enumerate(infos):
+                    if r == self.rank:
+                        tabs.append(weight.data_ptr())
+                        continue
+                    base = _OPENED.get(h)
+                    if base is None:
+                        p = C.c_void_p()
+                        L.call("b200_symm_import", (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p), launches=0)
+                        base = _OPENED[h] = p.value
+                    tabs.append(base + o)
+            except Exception:  # noqa: BLE001
+                tabs = None
+        oks = [None] * self.tp
+        dist.all_gather_object(oks, tabs is not None, group=self.group)
+        if not all(oks):
+            tabs = None
+        self._tables[key] = tabs
         return tabs
 
     def tables_barrier(self):

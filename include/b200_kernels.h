@@ -250,6 +250,14 @@ int b200_attn_bwd(const void* q, const void* k, const void* v, const void* out, 
                   long long q_sj, long long k_ss, long long k_sb, long long k_sg, long long dq_ss,
                   long long dq_sb, long long dq_sg, long long dq_sj, long long dk_ss, long long dk_sb,
                   long long dk_sg, float softmax_scale, int causal, cudaStream_t stream);
+/* Second-generation backward kernels (64-row streamed blocks, S / dP double-buffered in tensor memory): same
+ * contract, scratch and result; selected with B200_ATTN_BWD_ENTRY=b200_attn_bwd_v2 for A/B runs. */
+int b200_attn_bwd_v2(const void* q, const void* k, const void* v, const void* out, const void* dout,
+                     const float* lse, void* dq, void* dk, void* dv, float* scratch, int sq, int sk,
+                     int B, int G, int qpg, int hn, long long q_ss, long long q_sb, long long q_sg,
+                     long long q_sj, long long k_ss, long long k_sb, long long k_sg, long long dq_ss,
+                     long long dq_sb, long long dq_sg, long long dq_sj, long long dk_ss, long long dk_sb,
+                     long long dk_sg, float softmax_scale, int causal, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -246,3 +246,20 @@ def test_fused_reduce_gemm_tile_order_is_a_permutation_with_lag():
         # remote and own tiles alternate in the middle: the link is never asked for more than every other tile
         mid = seq[lag:2 * half - lag]
         assert all((a < half) != (b < half) for a, b in zip(mid, mid[1:]))
+
+
+def test_c_abi_header_sources_and_bindings_agree():
+    """Every exported entry point (B200_API in csrc/*.cu) is declared in include/b200_kernels.h, and every
+    ctypes binding of ops/lib.py names an entry point that exists."""
+    import re
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    src = set()
+    for f in (root / "epfl_megatron_b200" / "csrc").glob("*.cu"):
+        src |= set(re.findall(r"B200_API\s+[\w\s\*]+?\b(b200_\w+)\s*\(", f.read_text()))
+    hdr = set(re.findall(r"\b(b200_\w+)\s*\(", (root / "include" / "b200_kernels.h").read_text()))
+    bound = set(re.findall(r'"(b200_\w+)"\s*:', (root / "epfl_megatron_b200" / "ops" / "lib.py").read_text()))
+    assert len(src) > 60
+    assert not (src - hdr), f"exported but not declared in the header: {sorted(src - hdr)}"
+    assert not (hdr - src), f"declared but not defined: {sorted(hdr - src)}"
+    assert not (bound - src), f"bound in lib.py but not defined: {sorted(bound - src)}"

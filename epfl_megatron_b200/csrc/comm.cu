@@ -47,9 +47,11 @@ __global__ void copy2_kernel(const uint4* __restrict__ src, uint4* __restrict__ 
 
 constexpr int kStageBlocks = 148 * 4;
 
-// One launch per all-gather: (1) wait until every peer has pulled the previous content of this
-// staging shard, (2) copy the local rows into the staging shard (peers pull from there) and into
-// their place in the gathered matrix, (3) the last block to finish tells the peers "epoch e ready".
+// Stand-alone staging for kernels that pull rows themselves (parallel/symm.py gather_begin, e.g. the
+// embedding backward; the all-gather GEMM stages inside its own kernel): (1) wait until every peer has
+// pulled the previous content of this staging shard, (2) copy the local rows into the staging shard
+// (peers pull from there) and, when asked, into a second destination, (3) the last block to finish
+// tells the peers "epoch e ready".
 __global__ void stage_shard_kernel(const uint4* __restrict__ src, uint4* __restrict__ stage,
                                    uint4* __restrict__ own_rows, long long n16,
                                    const unsigned* consumed, int tp, int rank, unsigned wait_value,

@@ -15,6 +15,11 @@ over the bf16 tensor, which also produces its amax). Scaling is DELAYED as in Tr
 cast of step t uses a scale derived from the amax history of earlier steps
 (``scale = fp8_max / amax / 2**margin``, amax = most recent or the max over the history), everything
 stays on the device: scales and their inverses live in one pool tensor that the GEMM epilogue reads.
+
+The scaling state is NOT written to checkpoints (Transformer Engine stores it as ``_extra_state``): the
+first step of a process, fresh or resumed, scales every cast by the tensor's own amax (one extra
+reduction per cast) and seeds the history from there, so a resumed run needs no state. FP8 layers
+keep NCCL collectives under tensor parallelism (the in-kernel collectives are bf16 kernels).
 """
 from __future__ import annotations
 

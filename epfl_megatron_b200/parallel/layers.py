@@ -190,6 +190,16 @@ class _FusedVocabEmbedding(torch.autograd.Function):
         arr = (ctypes.c_void_p * 8)(*tabs)
         Fn.L.call("b200_embed_fwd", ids.data_ptr(), arr, out.data_ptr(), S, B, s_off, s_out, H, Vp, tp,
                   Fn.L.stream_ptr())
+        if tp > 1 and ws.verify:
+            # B200_COMM_VERIFY=1: masked local lookup + NCCL all-reduce, the reference's formulation
+            lo = rank * Vp
+            mask = (ids < lo) | (ids >= lo + Vp)
+            part = F.embedding((ids - lo).masked_fill(mask, 0), weight).masked_fill(mask.unsqueeze(-1), 0.0)
+            dist.all_reduce(part, group=state.get_tensor_model_parallel_group())
+            want = part.transpose(0, 1)[s_off:s_off + s_out]
+            if not torch.equal(out, want):
+                raise RuntimeError(f"peer-memory embedding (rank {rank}): {(out != want).sum().item()} elements "
+                                   "differ from lookup + all-reduce")
         ctx.save_for_backward(ids)
         ctx.weight_ref = weight
         ctx.sp = sequence_parallel

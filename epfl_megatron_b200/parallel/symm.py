@@ -347,6 +347,17 @@ class TPWorkspace:
         lse = torch.empty(T, device=self.device, dtype=torch.float32)
         L.call("b200_xent_combine_wait", self._xent(self.rank, s), self._flag(self.rank, self.w_xent_cnt + s),
                self._xent_target[s], loss.data_ptr(), lse.data_ptr(), T, self.tp, st)
+        if self.verify:
+            # B200_COMM_VERIFY=1: the same statistics through ONE NCCL all-gather and the plain combine kernel
+            stats = torch.empty(T, 3, device=self.device, dtype=torch.float32)
+            L.call("b200_xent_stats", logits2d.data_ptr(), labels.data_ptr(), stats.data_ptr(), T, V, vocab_start, st)
+            allst = torch.empty(self.tp * T, 3, device=self.device, dtype=torch.float32)
+            dist.all_gather_into_tensor(allst, stats, group=self.group)
+            want, want_lse = torch.empty_like(loss), torch.empty_like(lse)
+            L.call("b200_xent_combine", allst.data_ptr(), want.data_ptr(), want_lse.data_ptr(), T, self.tp, st)
+            if not (torch.allclose(loss, want, rtol=1e-5, atol=1e-5) and torch.allclose(lse, want_lse, rtol=1e-5, atol=1e-5)):
+                raise RuntimeError(f"cross-entropy exchange over peer memory (call {self.xent_calls}, rank {self.rank}): "
+                                   f"max loss difference {(loss - want).abs().max().item()} against NCCL")
         return loss, lse
 
     def check(self):

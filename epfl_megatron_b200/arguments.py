@@ -403,7 +403,8 @@ def validate_args(args, defaults=None):
     # The reference requires --transformer_impl transformer_engine for FP8 (arguments.py:304-306); here the
     # local layers run the same recipe on the library's own 8-bit GEMM (ops/fp8.py), so both spellings work.
     if args.fp8_e4m3 or args.fp8_hybrid:
-        _require(args.bf16, "fp8 training runs on bf16 parameters (--bf16)")
+        _require(args.bf16 or os.environ.get("B200_FP8_EMULATE") == "1",
+                 "fp8 training runs on bf16 parameters (--bf16)")
     _require(not (args.fp8_e4m3 and args.fp8_hybrid), "both fp8 formats")
     if args.recompute_granularity == "selective":
         _require(args.recompute_method is None, "recompute method not supported with selective")

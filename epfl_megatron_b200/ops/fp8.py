@@ -36,6 +36,10 @@ X, W, G = 0, 1, 2
 # instead of the delayed scale; useful when statistics move fast (the first steps of a run, tiny
 # synthetic benchmarks), not part of the reference's Transformer Engine recipe.
 _CURRENT_SCALING = os.environ.get("B200_FP8_CURRENT_SCALING", "0") == "1"
+# B200_FP8_EMULATE=1: the casts and GEMMs below are restated with torch's float8 dtypes (any device), so
+# the whole recipe -- scale bookkeeping, amax histories, weight-cast caching, the three GEMMs of a layer --
+# runs on CPU / Gloo through the real model code (tests/test_fp8_recipe_cpu.py).
+_EMULATE = os.environ.get("B200_FP8_EMULATE", "0") == "1"
 _CAP = 4096
 _POOL = None            # dict of pool tensors, created on first use
 _N = 0                  # metas registered
@@ -95,7 +99,9 @@ class Meta:
 def attach(weight, args):
     """Give ``weight`` an FP8 meta when the arguments ask for FP8 and the library can run it."""
     recipe = recipe_from_args(args)
-    if recipe is None or not weight.is_cuda or weight.dtype != torch.bfloat16 or not L.available():
+    if recipe is None:
+        return None
+    if not _EMULATE and (not weight.is_cuda or weight.dtype != torch.bfloat16 or not L.available()):
         return None
     if weight.shape[0] % 16 or weight.shape[1] % 16:
         return None
@@ -127,9 +133,11 @@ def advance_step():
 def quantize(x2d, meta: Meta, role, transpose, track_amax=True):
     """bf16 [rows, cols] -> (fp8 [rows, cols], fp8 [cols, rows] or None) with the role's current scale."""
     rows, cols = x2d.shape
+    e5m2 = int(role == G and meta.recipe.hybrid)
+    if _EMULATE:
+        return _quantize_emulated(x2d, meta, role, transpose, track_amax, e5m2)
     y = torch.empty(rows, cols, device=x2d.device, dtype=torch.uint8)
     yT = torch.empty(cols, rows, device=x2d.device, dtype=torch.uint8) if transpose else None
-    e5m2 = int(role == G and meta.recipe.hybrid)
     if (_STEP == 0 or _CURRENT_SCALING) and track_amax:
         # No history yet: the very first step scales by the tensor's own amax (two extra small device ops)
         # instead of the neutral scale 1, which would flush bf16-sized gradients to zero in E5M2.
@@ -143,8 +151,27 @@ def quantize(x2d, meta: Meta, role, transpose, track_amax=True):
     return y, yT
 
 
+def _quantize_emulated(x2d, meta, role, transpose, track_amax, e5m2):
+    """torch restatement of b200_fp8_quantize: same scale, same saturation, same amax update."""
+    xf = x2d.detach().float()
+    am = xf.abs().amax()
+    if (_STEP == 0 or _CURRENT_SCALING) and track_amax:
+        sc = meta.pool["fmax"][role] / am / (2.0 ** meta.recipe.margin)
+        sc = torch.where(torch.isfinite(sc) & (sc > 0), sc, torch.ones_like(sc))
+        meta.pool["scale"][meta.i, role] = sc
+        meta.pool["scale_inv"][meta.i, role] = 1.0 / sc
+    if track_amax:
+        h = meta.pool["hist"]
+        h[meta.i, role, 0] = torch.maximum(h[meta.i, role, 0], am)
+    lim, dt = (E5M2_MAX, torch.float8_e5m2) if e5m2 else (E4M3_MAX, torch.float8_e4m3fn)
+    y = (xf * meta.pool["scale"][meta.i, role]).clamp(-lim, lim).to(dt)
+    return y, (y.t().contiguous() if transpose else None)
+
+
 def usable(x2d, weight) -> bool:
     m = getattr(weight, "_b200_fp8", None)
+    if _EMULATE:
+        return m is not None and x2d.dim() == 2 and x2d.is_floating_point()
     return (m is not None and x2d.is_cuda and x2d.dtype == torch.bfloat16 and x2d.dim() == 2
             and x2d.shape[0] % 16 == 0 and x2d.shape[1] % 16 == 0 and x2d.stride(1) == 1 and x2d.stride(0) % 8 == 0)
 
@@ -156,9 +183,19 @@ def _weights(weight, meta: Meta):
     return meta.w8, meta.wT8
 
 
-def _gemm(a8, b8, out, M, N, K, a_e5m2, b_e5m2, out_mode, pa, pb):
+def _gemm(a8, b8, out, M, N, K, a_e5m2, b_e5m2, out_mode, meta, role_a, role_b):
+    """out (bf16 store: 0, fp32 store: 1, fp32 accumulate: 2) = A B^T / (scale_a * scale_b)."""
+    if _EMULATE:
+        inv = meta.pool["scale_inv"]
+        res = (a8.float() @ b8.float().t()) * (inv[meta.i, role_a] * inv[meta.i, role_b])
+        if out_mode == 2:
+            out.add_(res.to(out.dtype))
+        else:
+            out.copy_(res.to(out.dtype))
+        return out
     L.call("b200_gemm_fp8", a8.data_ptr(), b8.data_ptr(), out.data_ptr(), M, N, K, int(a_e5m2), int(b_e5m2),
-           a8.stride(0), b8.stride(0), out.stride(0), out_mode, pa, pb, L.stream_ptr())
+           a8.stride(0), b8.stride(0), out.stride(0), out_mode, meta.inv_ptr(role_a), meta.inv_ptr(role_b),
+           L.stream_ptr())
     return out
 
 
@@ -169,8 +206,8 @@ def forward_gemm(x2d, weight):
     w8, _ = _weights(weight, meta)
     M, K = x2d.shape
     N = weight.shape[0]
-    out = torch.empty(M, N, device=x2d.device, dtype=torch.bfloat16)
-    return _gemm(x8, w8, out, M, N, K, 0, 0, 0, meta.inv_ptr(X), meta.inv_ptr(W))
+    out = torch.empty(M, N, device=x2d.device, dtype=x2d.dtype)
+    return _gemm(x8, w8, out, M, N, K, 0, 0, 0, meta, X, W)
 
 
 def dgrad_gemm(dy2d, weight):
@@ -180,8 +217,8 @@ def dgrad_gemm(dy2d, weight):
     _, wT8 = _weights(weight, meta)
     M, N = dy2d.shape
     K = weight.shape[1]
-    dx = torch.empty(M, K, device=dy2d.device, dtype=torch.bfloat16)
-    _gemm(dy8, wT8, dx, M, K, N, meta.recipe.hybrid, 0, 0, meta.inv_ptr(G), meta.inv_ptr(W))
+    dx = torch.empty(M, K, device=dy2d.device, dtype=dy2d.dtype)
+    _gemm(dy8, wT8, dx, M, K, N, meta.recipe.hybrid, 0, 0, meta, G, W)
     return dx, dyT8
 
 
@@ -192,8 +229,7 @@ def wgrad_gemm(dyT8, x2d, weight, main_grad, accumulate):
     _, xT8 = quantize(x2d, meta, X, True, track_amax=False)
     N, M = dyT8.shape
     K = x2d.shape[1]
-    return _gemm(dyT8, xT8, main_grad, N, K, M, meta.recipe.hybrid, 0, 2 if accumulate else 1,
-                 meta.inv_ptr(G), meta.inv_ptr(X))
+    return _gemm(dyT8, xT8, main_grad, N, K, M, meta.recipe.hybrid, 0, 2 if accumulate else 1, meta, G, X)
 
 
 def reset():

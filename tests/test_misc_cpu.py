@@ -263,3 +263,50 @@ def test_c_abi_header_sources_and_bindings_agree():
     assert not (src - hdr), f"exported but not declared in the header: {sorted(src - hdr)}"
     assert not (hdr - src), f"declared but not defined: {sorted(hdr - src)}"
     assert not (bound - src), f"bound in lib.py but not defined: {sorted(bound - src)}"
+
+
+def test_fp8_gpu_path_python_side_with_recording_library(monkeypatch):
+    """The non-emulated FP8 path (the one a GPU runs) with the native calls recorded instead of executed:
+    every Python line between the autograd function and the C entry points runs, and the arguments are the
+    ones the entry points document (operand roles, formats, strides, output modes, scale pointers)."""
+    import torch
+    from epfl_megatron_b200.ops import fp8
+    fp8.reset()
+    calls = []
+    monkeypatch.setattr(fp8, "_EMULATE", False)
+    monkeypatch.setattr(fp8.L, "call", lambda name, *a, **k: calls.append((name, a)) or 0)
+    monkeypatch.setattr(fp8.L, "stream_ptr", lambda: 0)
+    try:
+        recipe = fp8.Recipe(hybrid=True, history_len=2, algo="max")
+        w = torch.zeros(48, 32, dtype=torch.bfloat16)
+        w._b200_fp8 = meta = fp8.Meta(torch.device("cpu"), recipe)
+        x = torch.zeros(64, 32, dtype=torch.bfloat16)
+        dy = torch.zeros(64, 48, dtype=torch.bfloat16)
+        y = fp8.forward_gemm(x, w)
+        assert y.shape == (64, 48) and y.dtype == torch.bfloat16
+        q_x, q_w, g_fwd = calls
+        assert q_x[0] == q_w[0] == "b200_fp8_quantize" and g_fwd[0] == "b200_gemm_fp8"
+        assert q_x[1][3:6] == (64, 32, 32) and q_x[1][2] is None and q_x[1][8] == 0          # no transpose, E4M3
+        assert q_w[1][3:6] == (48, 32, 32) and q_w[1][2] is not None                          # weight + transpose
+        assert q_x[1][6] == meta.scale_ptr(fp8.X) and q_x[1][7] == meta.amax_ptr(fp8.X)
+        assert g_fwd[1][3:8] == (64, 48, 32, 0, 0) and g_fwd[1][8:12] == (32, 32, 48, 0)
+        assert g_fwd[1][12:14] == (meta.inv_ptr(fp8.X), meta.inv_ptr(fp8.W))
+        calls.clear()
+        dx, dyT8 = fp8.dgrad_gemm(dy, w)                       # weights cached: one cast + one GEMM
+        assert [c[0] for c in calls] == ["b200_fp8_quantize", "b200_gemm_fp8"]
+        assert dx.shape == (64, 32) and dyT8.shape == (48, 64)
+        assert calls[0][1][8] == 1 and calls[0][1][6] == meta.scale_ptr(fp8.G)                # E5M2 gradients
+        assert calls[1][1][3:8] == (64, 32, 48, 1, 0) and calls[1][1][8:12] == (48, 48, 32, 0)
+        assert calls[1][1][12:14] == (meta.inv_ptr(fp8.G), meta.inv_ptr(fp8.W))
+        calls.clear()
+        main = torch.zeros(48, 32)
+        fp8.wgrad_gemm(dyT8, x, w, main, accumulate=True)
+        assert calls[0][1][7] is None, "the re-cast of x for the weight gradient must not touch the amax history"
+        assert calls[1][1][3:8] == (48, 32, 64, 1, 0) and calls[1][1][11] == 2
+        assert calls[1][1][12:14] == (meta.inv_ptr(fp8.G), meta.inv_ptr(fp8.X))
+        calls.clear()
+        fp8.advance_step()
+        fp8.forward_gemm(x, w)                                 # new optimizer step: the weight is cast again
+        assert [c[0] for c in calls].count("b200_fp8_quantize") == 2
+    finally:
+        fp8.reset()
